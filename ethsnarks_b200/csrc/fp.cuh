@@ -1,0 +1,280 @@
+// 254-bit prime-field arithmetic for BN254 (Fr and Fq) on sm_100a: 8 x 32-bit limbs, Montgomery form, R = 2^256.
+//
+// Replaces (B200-native, not a translation) the reference's libff::Fp_model<4, modulus>:
+//   mul_reduce  FF/algebra/fields/fp.tcc:23-186      add :310-420   sub :423-510   as_bigint :228-238   inverse :642-692
+// (FF = /root/reference/depends/libsnark/depends/libff/libff).  Values are kept fully reduced in [0, p), so every
+// element has the same 32-byte representation as the reference's mont_repr (4 x u64 little-endian == 8 x u32).
+//
+// Multiplication is a CIOS Montgomery product whose partial products are issued as mad.lo.cc / madc.hi.cc pairs on
+// even/odd-aligned accumulators; ptxas fuses each pair into one IMAD.WIDE.U32.X (carry in a predicate), so one
+// product costs 128 wide multiply-adds + 8 IMAD.LO for the per-row quotient digit — the fma-heavy (IMAD) pipe is the
+// roofline for everything built on this file.
+#pragma once
+#include <cstdint>
+
+namespace b200 {
+
+#define B200_DEV __device__ __forceinline__
+
+struct FrParams {
+    // r = 21888242871839275222246405745257275088548364400416034343698204186575808495617 (mcl_bn128_init.cpp:41)
+    static __host__ __device__ constexpr uint32_t mod(int i) {
+        constexpr uint32_t m[8] = {0xf0000001u, 0x43e1f593u, 0x79b97091u, 0x2833e848u, 0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return m[i];
+    }
+    static __host__ __device__ constexpr uint32_t one(int i) {   // R mod r
+        constexpr uint32_t m[8] = {0x4ffffffbu, 0xac96341cu, 0x9f60cd29u, 0x36fc7695u, 0x7879462eu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return m[i];
+    }
+    static __host__ __device__ constexpr uint32_t r2(int i) {    // R^2 mod r
+        constexpr uint32_t m[8] = {0xae216da7u, 0x1bb8e645u, 0xe35c59e3u, 0x53fe3ab1u, 0x53bb8085u, 0x8c49833du, 0x7f4e44a5u, 0x0216d0b1u};
+        return m[i];
+    }
+    static constexpr uint32_t INV = 0xefffffffu;   // -r^{-1} mod 2^32
+};
+
+struct FqParams {
+    // q = 21888242871839275222246405745257275088696311157297823662689037894645226208583 (mcl_bn128_init.cpp:67)
+    static __host__ __device__ constexpr uint32_t mod(int i) {
+        constexpr uint32_t m[8] = {0xd87cfd47u, 0x3c208c16u, 0x6871ca8du, 0x97816a91u, 0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return m[i];
+    }
+    static __host__ __device__ constexpr uint32_t one(int i) {
+        constexpr uint32_t m[8] = {0xc58f0d9du, 0xd35d438du, 0xf5c70b3du, 0x0a78eb28u, 0x7879462cu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return m[i];
+    }
+    static __host__ __device__ constexpr uint32_t r2(int i) {
+        constexpr uint32_t m[8] = {0x538afa89u, 0xf32cfc5bu, 0xd44501fbu, 0xb5e71911u, 0x0a417ff6u, 0x47ab1effu, 0xcab8351fu, 0x06d89f71u};
+        return m[i];
+    }
+    static constexpr uint32_t INV = 0xe4866389u;
+};
+
+// ---- carry-chain building blocks (each chain is ONE asm statement so the CC flag never crosses a statement) ----
+
+// acc(8 limbs) += {a0,a1,a2,a3} (x) b laid out as four 64-bit products at limb offsets 0,2,4,6; carry-out added to `top`.
+B200_DEV void chain_mad_carry(uint32_t* acc, uint32_t& top, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b) {
+    asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\t"
+        "madc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %2;\n\t"
+        "madc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %4;\n\t"
+        "madc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, %6;\n\t"
+        "madc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+        "addc.u32 %8, %8, 0;"
+        : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]), "+r"(acc[6]), "+r"(acc[7]), "+r"(top)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+}
+// same without a carry-out (caller guarantees none)
+B200_DEV void chain_mad(uint32_t* acc, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b) {
+    asm("mad.lo.cc.u32 %0, %8, %12, %0;\n\t"
+        "madc.hi.cc.u32 %1, %8, %12, %1;\n\t"
+        "madc.lo.cc.u32 %2, %9, %12, %2;\n\t"
+        "madc.hi.cc.u32 %3, %9, %12, %3;\n\t"
+        "madc.lo.cc.u32 %4, %10, %12, %4;\n\t"
+        "madc.hi.cc.u32 %5, %10, %12, %5;\n\t"
+        "madc.lo.cc.u32 %6, %11, %12, %6;\n\t"
+        "madc.hi.u32 %7, %11, %12, %7;"
+        : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]), "+r"(acc[6]), "+r"(acc[7])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+}
+// x0 += y[1];  y = (y >> 64 bits) + {a0..a3} (x) b + carry(x0)      (the one-limb shift of the CIOS row, fused)
+B200_DEV void chain_shift_mad(uint32_t* y, uint32_t& x0, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b) {
+    asm("add.cc.u32 %8, %8, %1;\n\t"
+        "madc.lo.cc.u32 %0, %9, %13, %2;\n\t"
+        "madc.hi.cc.u32 %1, %9, %13, %3;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %4;\n\t"
+        "madc.hi.cc.u32 %3, %10, %13, %5;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %6;\n\t"
+        "madc.hi.cc.u32 %5, %11, %13, %7;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, 0;\n\t"
+        "madc.hi.u32 %7, %12, %13, 0;"
+        : "+r"(y[0]), "+r"(y[1]), "+r"(y[2]), "+r"(y[3]), "+r"(y[4]), "+r"(y[5]), "+r"(y[6]), "+r"(y[7]), "+r"(x0)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+}
+
+template <typename P>
+struct __align__(16) Fp {
+    uint32_t v[8];
+
+    static B200_DEV Fp zero() { Fp r; _Pragma("unroll") for (int i = 0; i < 8; ++i) r.v[i] = 0; return r; }
+    static B200_DEV Fp one() { Fp r; _Pragma("unroll") for (int i = 0; i < 8; ++i) r.v[i] = P::one(i); return r; }
+    static B200_DEV Fp r2() { Fp r; _Pragma("unroll") for (int i = 0; i < 8; ++i) r.v[i] = P::r2(i); return r; }
+
+    B200_DEV bool is_zero() const {
+        uint32_t o = 0;
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) o |= v[i];
+        return o == 0;
+    }
+    B200_DEV bool operator==(const Fp& b) const {
+        uint32_t o = 0;
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) o |= v[i] ^ b.v[i];
+        return o == 0;
+    }
+    B200_DEV bool operator!=(const Fp& b) const { return !(*this == b); }
+
+    // r = (r >= p) ? r - p : r     (r < 2p)
+    B200_DEV void reduce_once() {
+        uint32_t t[8], borrow;
+        asm("sub.cc.u32 %0, %9, %17;\n\t"
+            "subc.cc.u32 %1, %10, %18;\n\t"
+            "subc.cc.u32 %2, %11, %19;\n\t"
+            "subc.cc.u32 %3, %12, %20;\n\t"
+            "subc.cc.u32 %4, %13, %21;\n\t"
+            "subc.cc.u32 %5, %14, %22;\n\t"
+            "subc.cc.u32 %6, %15, %23;\n\t"
+            "subc.cc.u32 %7, %16, %24;\n\t"
+            "subc.u32 %8, 0, 0;"
+            : "=r"(t[0]), "=r"(t[1]), "=r"(t[2]), "=r"(t[3]), "=r"(t[4]), "=r"(t[5]), "=r"(t[6]), "=r"(t[7]), "=r"(borrow)
+            : "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+              "r"(P::mod(0)), "r"(P::mod(1)), "r"(P::mod(2)), "r"(P::mod(3)), "r"(P::mod(4)), "r"(P::mod(5)), "r"(P::mod(6)), "r"(P::mod(7)));
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) v[i] = borrow ? v[i] : t[i];
+    }
+
+    friend B200_DEV Fp operator+(const Fp& a, const Fp& b) {
+        Fp r;
+        asm("add.cc.u32 %0, %8, %16;\n\t"
+            "addc.cc.u32 %1, %9, %17;\n\t"
+            "addc.cc.u32 %2, %10, %18;\n\t"
+            "addc.cc.u32 %3, %11, %19;\n\t"
+            "addc.cc.u32 %4, %12, %20;\n\t"
+            "addc.cc.u32 %5, %13, %21;\n\t"
+            "addc.cc.u32 %6, %14, %22;\n\t"
+            "addc.u32 %7, %15, %23;"
+            : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+            : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+              "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+        r.reduce_once();   // a + b < 2p < 2^255: no carry out of limb 7
+        return r;
+    }
+    friend B200_DEV Fp operator-(const Fp& a, const Fp& b) {
+        Fp r;
+        uint32_t borrow;
+        asm("sub.cc.u32 %0, %9, %17;\n\t"
+            "subc.cc.u32 %1, %10, %18;\n\t"
+            "subc.cc.u32 %2, %11, %19;\n\t"
+            "subc.cc.u32 %3, %12, %20;\n\t"
+            "subc.cc.u32 %4, %13, %21;\n\t"
+            "subc.cc.u32 %5, %14, %22;\n\t"
+            "subc.cc.u32 %6, %15, %23;\n\t"
+            "subc.cc.u32 %7, %16, %24;\n\t"
+            "subc.u32 %8, 0, 0;"
+            : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]), "=r"(borrow)
+            : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+              "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+        // borrow is 0 or 0xffffffff: add back p & borrow
+        asm("add.cc.u32 %0, %0, %8;\n\t"
+            "addc.cc.u32 %1, %1, %9;\n\t"
+            "addc.cc.u32 %2, %2, %10;\n\t"
+            "addc.cc.u32 %3, %3, %11;\n\t"
+            "addc.cc.u32 %4, %4, %12;\n\t"
+            "addc.cc.u32 %5, %5, %13;\n\t"
+            "addc.cc.u32 %6, %6, %14;\n\t"
+            "addc.u32 %7, %7, %15;"
+            : "+r"(r.v[0]), "+r"(r.v[1]), "+r"(r.v[2]), "+r"(r.v[3]), "+r"(r.v[4]), "+r"(r.v[5]), "+r"(r.v[6]), "+r"(r.v[7])
+            : "r"(P::mod(0) & borrow), "r"(P::mod(1) & borrow), "r"(P::mod(2) & borrow), "r"(P::mod(3) & borrow),
+              "r"(P::mod(4) & borrow), "r"(P::mod(5) & borrow), "r"(P::mod(6) & borrow), "r"(P::mod(7) & borrow));
+        return r;
+    }
+    B200_DEV Fp neg() const { return is_zero() ? *this : (zero() - *this); }
+    B200_DEV Fp dbl() const { return *this + *this; }
+
+    // Montgomery product a*b*R^-1 mod p, fully reduced.
+    friend B200_DEV Fp operator*(const Fp& a, const Fp& b) {
+        uint32_t E[8], O[8];
+        // row 0: E = a_even (x) b0, O = a_odd (x) b0 (O's limb k has weight 2^(32(k+1)))
+        _Pragma("unroll") for (int j = 0; j < 8; j += 2) {
+            uint64_t te = (uint64_t)a.v[j] * b.v[0], to = (uint64_t)a.v[j + 1] * b.v[0];
+            E[j] = (uint32_t)te; E[j + 1] = (uint32_t)(te >> 32);
+            O[j] = (uint32_t)to; O[j + 1] = (uint32_t)(to >> 32);
+        }
+        uint32_t m = E[0] * P::INV;
+        chain_mad(O, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+        chain_mad_carry(E, O[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+        _Pragma("unroll") for (int i = 1; i < 8; ++i) {
+            uint32_t* X = (i & 1) ? O : E;   // even-aligned role this row
+            uint32_t* Y = (i & 1) ? E : O;   // odd-aligned role (holds last row's even array, limb 0 == 0)
+            chain_shift_mad(Y, X[0], a.v[1], a.v[3], a.v[5], a.v[7], b.v[i]);
+            chain_mad_carry(X, Y[7], a.v[0], a.v[2], a.v[4], a.v[6], b.v[i]);
+            m = X[0] * P::INV;
+            chain_mad(Y, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+            chain_mad_carry(X, Y[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+        }
+        // after row 7: X = O, Y = E; result = Y + (X >> 32)
+        Fp r;
+        asm("add.cc.u32 %0, %8, %16;\n\t"
+            "addc.cc.u32 %1, %9, %17;\n\t"
+            "addc.cc.u32 %2, %10, %18;\n\t"
+            "addc.cc.u32 %3, %11, %19;\n\t"
+            "addc.cc.u32 %4, %12, %20;\n\t"
+            "addc.cc.u32 %5, %13, %21;\n\t"
+            "addc.cc.u32 %6, %14, %22;\n\t"
+            "addc.u32 %7, %15, 0;"
+            : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+            : "r"(E[0]), "r"(E[1]), "r"(E[2]), "r"(E[3]), "r"(E[4]), "r"(E[5]), "r"(E[6]), "r"(E[7]),
+              "r"(O[1]), "r"(O[2]), "r"(O[3]), "r"(O[4]), "r"(O[5]), "r"(O[6]), "r"(O[7]));
+        r.reduce_once();
+        return r;
+    }
+    B200_DEV Fp sqr() const { return (*this) * (*this); }
+
+    B200_DEV Fp to_mont() const { return (*this) * r2(); }
+    B200_DEV Fp from_mont() const {   // as_bigint: Montgomery-multiply by 1
+        Fp o = zero(); o.v[0] = 1;
+        return (*this) * o;
+    }
+    // this^e for a 32-bit exponent (left-to-right)
+    B200_DEV Fp pow_u32(uint32_t e) const {
+        Fp r = one();
+        for (int i = 31; i >= 0; --i) {
+            r = r.sqr();
+            if ((e >> i) & 1) r = r * (*this);
+        }
+        return r;
+    }
+    // Fermat inverse this^(p-2); 0 -> 0.  (The reference uses binary extended GCD, fp.tcc:642-692; same value.)
+    B200_DEV Fp inv() const {
+        Fp r = one();
+        for (int i = 7; i >= 0; --i) {
+            uint32_t w = P::mod(i) - (i == 0 ? 2u : 0u);   // low limb of p is > 2 for both fields
+            for (int bit = 31; bit >= 0; --bit) {
+                r = r.sqr();
+                if ((w >> bit) & 1) r = r * (*this);
+            }
+        }
+        return r;
+    }
+};
+
+typedef Fp<FrParams> Fr;
+typedef Fp<FqParams> Fq;
+
+// Fq2 = Fq[u]/(u^2 + 1): a + b*u   (mcl Fp2T{a,b}, MCL/include/mcl/fp_tower.hpp:199-225; libff c0 + c1*u, fp2.tcc)
+struct Fq2 {
+    Fq a, b;
+    static B200_DEV Fq2 zero() { return Fq2{Fq::zero(), Fq::zero()}; }
+    static B200_DEV Fq2 one() { return Fq2{Fq::one(), Fq::zero()}; }
+    B200_DEV bool is_zero() const { return a.is_zero() && b.is_zero(); }
+    B200_DEV bool operator==(const Fq2& o) const { return a == o.a && b == o.b; }
+    B200_DEV bool operator!=(const Fq2& o) const { return !(*this == o); }
+    friend B200_DEV Fq2 operator+(const Fq2& x, const Fq2& y) { return Fq2{x.a + y.a, x.b + y.b}; }
+    friend B200_DEV Fq2 operator-(const Fq2& x, const Fq2& y) { return Fq2{x.a - y.a, x.b - y.b}; }
+    B200_DEV Fq2 neg() const { return Fq2{a.neg(), b.neg()}; }
+    B200_DEV Fq2 dbl() const { return Fq2{a.dbl(), b.dbl()}; }
+    friend B200_DEV Fq2 operator*(const Fq2& x, const Fq2& y) {   // Karatsuba, 3 Fq products
+        Fq aa = x.a * y.a, bb = x.b * y.b;
+        Fq m = (x.a + x.b) * (y.a + y.b);
+        return Fq2{aa - bb, m - aa - bb};
+    }
+    B200_DEV Fq2 sqr() const {   // complex squaring, 2 Fq products
+        Fq ab = a * b;
+        return Fq2{(a + b) * (a - b), ab.dbl()};
+    }
+    B200_DEV Fq2 inv() const {
+        Fq n = (a.sqr() + b.sqr()).inv();
+        return Fq2{a * n, (b * n).neg()};
+    }
+};
+
+}  // namespace b200

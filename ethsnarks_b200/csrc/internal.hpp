@@ -1,0 +1,115 @@
+// Internal host-side interface between the translation units of libb200snark.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstddef>
+#include <string>
+#include <vector>
+#include <map>
+#include <stdexcept>
+
+struct b200_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string last_error;
+    int sm_count = 148;
+    // growable named scratch buffers (device), reused across calls
+    struct Slot { void* p = nullptr; size_t cap = 0; };
+    std::map<std::string, Slot> slots;
+    // phase timings of the last prove / msm / h call (CUDA events on `stream`)
+    std::vector<std::pair<std::string, std::pair<cudaEvent_t, cudaEvent_t>>> timing_events;
+    std::vector<std::pair<std::string, float>> timings;
+    bool timing_enabled = true;
+    unsigned long long launches = 0;   // kernels launched by this library since init
+    int window_override = 0;           // 0 = cost model
+    int chunk_override = 0;            // 0 = auto
+
+    void* scratch(const char* name, size_t bytes);   // throws std::runtime_error on failure
+    void t_begin(const char* name);
+    void t_end();
+    void t_collect();
+};
+
+#define B200_CUDA_CHECK(expr)                                                                                   \
+    do {                                                                                                        \
+        cudaError_t _e = (expr);                                                                                \
+        if (_e != cudaSuccess)                                                                                  \
+            throw std::runtime_error(std::string(#expr) + ": " + cudaGetErrorString(_e) + " @" + __FILE__ + ":" + \
+                                     std::to_string(__LINE__));                                                 \
+    } while (0)
+
+namespace b200 {
+
+// --- msm.cu ---------------------------------------------------------------------------------------------------
+// Device-resident inputs; result is ONE XYZZ point written to d_out (G1: 4x32 B, G2: 4x64 B).
+//   group: 1 = G1, 2 = G2.  d_scalars: Fr elements (Montgomery if scalars_mont, else standard form), optionally
+//   gathered: scalar_i = d_scalars[d_gather[i]].  d_bases: affine Montgomery, (0,0) = infinity.
+#define B200_DECL_GROUP(SUFFIX)                                                                                                   \
+    void msm_run_##SUFFIX(b200_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_gather, size_t n,         \
+                          bool scalars_mont, void* d_out_xyzz);                                                                  \
+    void g_finish_##SUFFIX(b200_ctx* ctx, const void* d_xyzz_terms, int n_terms, const void* d_affine_terms, int n_affine,       \
+                           void* d_out_affine, bool to_std);                                                                     \
+    void g_fixed_base_##SUFFIX(b200_ctx* ctx, const void* d_scalars_mont, size_t n, void* d_out_affine);                         \
+    void g_add_affine_##SUFFIX(b200_ctx* ctx, const void* d_a, const void* d_b, void* d_out, size_t n);                          \
+    void g_scalar_mul_##SUFFIX(b200_ctx* ctx, const void* d_affine_base, const void* d_scalar_mont, void* d_out_xyzz);
+B200_DECL_GROUP(g1)
+B200_DECL_GROUP(g2)
+// g_finish: out = sum(xyzz terms) + sum(affine terms) normalised to affine (Montgomery, or standard form if to_std),
+//           written as the affine point followed by a u32 infinity flag.
+inline void msm_run(b200_ctx* c, int group, const void* b, const void* s, const uint32_t* g, size_t n, bool mont, void* out) {
+    if (group == 1) msm_run_g1(c, b, s, g, n, mont, out); else msm_run_g2(c, b, s, g, n, mont, out);
+}
+inline void g_finish(b200_ctx* c, int group, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {
+    if (group == 1) g_finish_g1(c, xt, nx, at, na, out, to_std); else g_finish_g2(c, xt, nx, at, na, out, to_std);
+}
+inline void g_fixed_base(b200_ctx* c, int group, const void* s, size_t n, void* out) {
+    if (group == 1) g_fixed_base_g1(c, s, n, out); else g_fixed_base_g2(c, s, n, out);
+}
+inline void g_add_affine(b200_ctx* c, int group, const void* a, const void* b, void* out, size_t n) {
+    if (group == 1) g_add_affine_g1(c, a, b, out, n); else g_add_affine_g2(c, a, b, out, n);
+}
+inline void g_scalar_mul(b200_ctx* c, int group, const void* base, const void* k, void* out) {
+    if (group == 1) g_scalar_mul_g1(c, base, k, out); else g_scalar_mul_g2(c, base, k, out);
+}
+
+// --- ntt.cu ---------------------------------------------------------------------------------------------------
+struct Domain {
+    uint32_t logm = 0;
+    void* tw_fwd = nullptr;    // omega^e, e < m/2           (Fr Montgomery)
+    void* tw_inv = nullptr;    // omega^-e
+    void* cs_fwd = nullptr;    // m^-1 * g^bitrev(p)         (post-scale of iNTT in bit-reversed order, feeds coset NTT)
+    void* cs_inv = nullptr;    // m^-1 * g^-bitrev(p)        (post-scale of the final icosetFFT, bit-reversed order)
+    void* zinv = nullptr;      // (g^m - 1)^-1, one element
+};
+void domain_create(b200_ctx* ctx, uint32_t logm, Domain* out);
+void domain_free(Domain* d);
+// in-place transforms on device data (natural order in/out): mode 0 FFT, 1 iFFT, 2 cosetFFT, 3 icosetFFT
+void ntt_natural(b200_ctx* ctx, const Domain& dom, void* d_data, int mode);
+// fused H chain: a, b, c hold the evaluations on S (natural order, m entries each); on return c holds the
+// coefficients of H in BIT-REVERSED order (c[p] = h[bitrev(p)]), a and b are clobbered.
+void h_chain(b200_ctx* ctx, const Domain& dom, void* d_a, void* d_b, void* d_c);
+void bitrev_permute(b200_ctx* ctx, const void* d_in, void* d_out, uint32_t logm, size_t elem_bytes);
+void field_op(b200_ctx* ctx, int field, int op, const void* d_a, const void* d_b, void* d_out, size_t n);
+
+// --- spmv (in ntt.cu) -----------------------------------------------------------------------------------------
+struct DeviceCsr {
+    uint64_t n_rows = 0, nnz = 0;
+    uint64_t* row_ptr = nullptr;
+    uint32_t* col = nullptr;
+    uint32_t* cidx = nullptr;
+    // long rows (length > LONG_ROW) are split into segments handled by a block each
+    uint32_t n_seg = 0;
+    uint32_t* seg_row = nullptr;     // row of each segment
+    uint64_t* seg_begin = nullptr;   // [n_seg + 1) nnz ranges (seg_begin[i]..seg_end[i])
+    uint64_t* seg_end = nullptr;
+    uint32_t n_long = 0;
+    uint32_t* long_row = nullptr;    // distinct long rows
+    uint32_t* long_seg0 = nullptr;   // [n_long + 1) first segment of each long row
+};
+void csr_upload(b200_ctx* ctx, const uint64_t* row_ptr, const uint32_t* col, const uint32_t* cidx, uint64_t n_rows, DeviceCsr* out);
+void csr_free(DeviceCsr* c);
+// out[row] = sum coeffs[cidx[k]] * w[col[k]]  for row < n_rows
+void spmv(b200_ctx* ctx, const DeviceCsr& M, const void* d_coeffs, const void* d_w, void* d_out);
+void witness_rows(b200_ctx* ctx, const void* d_w, void* d_a, void* d_b, void* d_c, uint64_t nc, uint64_t ni, uint64_t m);
+
+}  // namespace b200

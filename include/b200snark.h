@@ -1,0 +1,123 @@
+/* b200snark.h — C ABI of libb200snark.so: the B200 (sm_100a) Groth16 proving backend behind ethsnarks' prover.
+ *
+ * Every entry point replaces a piece of the reference's CPU prove path (paths relative to the reference tree;
+ * LS = depends/libsnark/libsnark, FF = depends/libsnark/depends/libff/libff, FQ = depends/libfqfft/libfqfft):
+ *
+ *   b200_key_load        ethsnarks::load_proving_key                    src/stubs.cpp:36-39, src/utils.hpp:176-185,
+ *                        operator>>(istream&, proving_key[_nozk]&)      src/r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.tcc:68-87,124-143
+ *   b200_circuit_load    ProverContext.constraint_system + get_domain   …zok.hpp:279-291, src/stubs.cpp:49-75
+ *   b200_prove           r1cs_gg_ppzksnark_zok_prover<ppT>               …zok.tcc:451-550  (r = s = NULL), and the r,s form of
+ *                        LS/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.tcc:389-503
+ *   b200_h               r1cs_to_qap_witness_map                         LS/reductions/r1cs_to_qap/r1cs_to_qap.tcc:217-302
+ *   b200_ntt             recursive_domain::{FFT,iFFT,cosetFFT,icosetFFT} FQ/evaluation_domain/domains/recursive_domain.tcc:102-142
+ *   b200_msm_g1/g2       libff::multi_exp / multi_exp_with_mixed_addition FF/algebra/scalar_multiplication/multiexp.tcc:595-714
+ *   b200_field_op        Fp_model mul / add / sub / as_bigint / inverse  FF/algebra/fields/fp.tcc:23-186,228-238,310-510,642-692
+ *   b200_g1_add/g2_add   G1/G2 ::add / mixed_add / dbl                   FF/algebra/curves/mcl_bn128/mcl_bn128_g1.cpp:136-164
+ *   b200_g1/g2_fixed_base  batch_exp (generator side)                    FF/algebra/scalar_multiplication/multiexp.tcc:838-905
+ *
+ * Conventions (the reference's existing C ABI precedent is src/verify_dll.cpp:3-10): plain pointers and sizes, all
+ * buffers caller-allocated, int status return (0 = ok), no ownership transfer except the opaque handles.
+ * Field elements are 4 x uint64 little-endian limbs.  "mont" = Montgomery form with R = 2^256, which is the
+ * reference's in-memory and key-file representation (Fp_model::mont_repr, MONTGOMERY_OUTPUT); "std" = the plain
+ * integer.  G1 affine = x,y (8 limbs); G2 affine = x.a, x.b, y.a, y.b (16 limbs; x = x.a + x.b*u, mcl order).
+ * One handle is bound to one CUDA device; calls on one handle must be serialised by the caller (the reference prover
+ * is not re-entrant either).  There is no CPU fallback: without a CUDA device b200_init fails with B200_ERR_CUDA.
+ */
+#ifndef B200SNARK_H_
+#define B200SNARK_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200_ctx b200_ctx;
+typedef struct b200_key b200_key;
+typedef struct b200_bases b200_bases;
+
+enum { B200_OK = 0, B200_ERR_CUDA = 1, B200_ERR_ARG = 2, B200_ERR_FORMAT = 3, B200_ERR_STATE = 4 };
+/* proving-key byte layouts: mcl points (default CURVE=MCL_BN128 build) or libff alt_bn128 points; "NOZK" =
+ * r1cs_gg_ppzksnark_zok_proving_key_nozk (B query in G2 only), "FULL" = …_proving_key (B query = G2,G1 pairs). */
+enum { B200_FMT_MCL_NOZK = 0, B200_FMT_MCL_FULL = 1, B200_FMT_ALT_NOZK = 2, B200_FMT_ALT_FULL = 3 };
+enum { B200_OP_MUL = 0, B200_OP_ADD = 1, B200_OP_SUB = 2, B200_OP_TO_MONT = 3, B200_OP_FROM_MONT = 4, B200_OP_INV = 5, B200_OP_SQR = 6, B200_OP_NEG = 7 };
+enum { B200_NTT_FFT = 0, B200_NTT_IFFT = 1, B200_NTT_COSET_FFT = 2, B200_NTT_ICOSET_FFT = 3 };
+
+/* One R1CS matrix in CSR form: row i holds sum_k coeff_table[coeff_idx[k]] * w[col[k]], k in [row_ptr[i], row_ptr[i+1]).
+ * col 0 is the constant ONE (protoboard values[0]); coeff_idx indexes the table given to b200_circuit_load, the
+ * flattened form of the reference's ConstantStorage (LS/relations/variable.hpp:47-86). */
+typedef struct {
+    const uint64_t* row_ptr;   /* n_rows + 1 */
+    const uint32_t* col;
+    const uint32_t* coeff_idx;
+    uint64_t n_rows;
+} b200_csr;
+
+int b200_init(const int* device_ids, int n_devices, b200_ctx** out);   /* n_devices must be 1 (one process per GPU) */
+void b200_shutdown(b200_ctx* ctx);
+const char* b200_strerror(int code);
+const char* b200_last_error(b200_ctx* ctx);
+void* b200_stream(b200_ctx* ctx);                        /* the cudaStream_t every kernel of this ctx is launched on */
+unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by this library on ctx since b200_init */
+int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing" */
+int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
+int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);
+
+/* ---- sub-operations (parity tests, config-5 MSM sweep) ---- */
+int b200_field_op(b200_ctx* ctx, int field /*0 Fr, 1 Fq*/, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
+int b200_g1_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf,
+                uint64_t* out_xy, uint8_t* out_inf, size_t n);
+int b200_g2_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf,
+                uint64_t* out_xy, uint8_t* out_inf, size_t n);
+int b200_g1_fixed_base(b200_ctx* ctx, const uint64_t* scalars_mont, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
+int b200_g2_fixed_base(b200_ctx* ctx, const uint64_t* scalars_mont, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
+int b200_ntt(b200_ctx* ctx, uint64_t* data_mont, uint32_t log_m, int mode);
+int b200_msm_g1(b200_ctx* ctx, const uint64_t* bases_xy_mont, const uint8_t* inf, const uint64_t* scalars_mont, size_t n,
+                uint64_t out_xy_mont[8], uint8_t* out_inf);
+int b200_msm_g2(b200_ctx* ctx, const uint64_t* bases_xy_mont, const uint8_t* inf, const uint64_t* scalars_mont, size_t n,
+                uint64_t out_xy_mont[16], uint8_t* out_inf);
+
+/* ---- device-resident base sets (what a loaded key holds; used directly by the MSM sweep) ---- */
+int b200_bases_upload(b200_ctx* ctx, int group /*1|2*/, const uint64_t* xy_mont, const uint8_t* inf, size_t n, b200_bases** out);
+int b200_bases_generate(b200_ctx* ctx, int group, const uint64_t* scalars_mont, size_t n, b200_bases** out); /* k_i * generator */
+int b200_bases_download(b200_bases* bases, uint64_t* xy_mont, uint8_t* inf);
+size_t b200_bases_count(b200_bases* bases);
+void b200_bases_free(b200_bases* bases);
+/* scalars on the host (copied inside the call) or already on the device (scalars_on_device != 0) */
+int b200_msm(b200_ctx* ctx, b200_bases* bases, const uint64_t* scalars_mont, size_t n, int scalars_on_device,
+             uint64_t* out_xy_mont, uint8_t* out_inf);
+
+/* ---- the prove path ---- */
+int b200_key_load(b200_ctx* ctx, const void* pk_bytes, size_t len, int fmt, b200_key** out);
+/* keep only this rank's 1/world slice of every query (multi-GPU: one process per GPU, see b200_prove_partial) */
+int b200_key_load_sharded(b200_ctx* ctx, const void* pk_bytes, size_t len, int fmt, int rank, int world, b200_key** out);
+/* a key assembled from resident base sets (synthetic keys for benchmarks); takes ownership of nothing, copies nothing:
+ * the base sets must outlive the key.  A_idx / B_idx: variable index of each A / B entry (NULL = identity). */
+int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b200_bases* B_g2, b200_bases* B_g1 /*may be NULL*/,
+                        const uint32_t* B_idx, b200_bases* H, b200_bases* L, const uint64_t* alpha_beta_delta_g1_xy /*3 x 8, mont*/,
+                        const uint64_t* beta_delta_g2_xy /*2 x 16, mont*/, uint64_t num_variables, uint64_t num_inputs,
+                        b200_key** out);
+void b200_key_free(b200_key* key);
+/* out[0..7]: domain_size (= num_variables + 1), |A|, |B|, |H|, |L| (this rank's counts), full(0/1), m, num_inputs */
+int b200_key_info(b200_key* key, uint64_t out[8]);
+int b200_circuit_load(b200_key* key, const b200_csr* A, const b200_csr* B, const b200_csr* C, const uint64_t* coeff_table_mont,
+                      size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables);
+/* witness = full assignment, 4 * (num_variables + 1) limbs, w[0] = 1, Montgomery.  r = s = NULL: the reference's
+ * no-ZK prover.  Outputs: affine, STANDARD form (ready for proof_to_json), infinity flags for A, B, C. */
+int b200_prove(b200_key* key, const uint64_t* witness_mont, const uint64_t r_mont[4], const uint64_t s_mont[4],
+               uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);
+/* coefficients of H, natural order, m entries (h[m-1] = 0), Montgomery */
+int b200_h(b200_key* key, const uint64_t* witness_mont, uint64_t* h_out_mont);
+/* evaluations of A, B, C on the domain S (m entries each, Montgomery): the witness-times-R1CS step alone */
+int b200_witness_eval(b200_key* key, const uint64_t* witness_mont, uint64_t* a_out, uint64_t* b_out, uint64_t* c_out);
+/* multi-GPU: this rank's partial sums over its key shard — evaluation_At, evaluation_Bt (G2), evaluation_Ht + Lt —
+ * as affine Montgomery points: partial[0..7] A, [8..23] B, [24..31] C; flags[3]. */
+int b200_prove_partial(b200_key* key, const uint64_t* witness_mont, uint64_t partial[32], uint8_t flags[3]);
+/* sums `world` partials (after an all-gather), adds alpha_g1 / beta_g2, returns the proof points in standard form */
+int b200_proof_combine(b200_key* key, const uint64_t* partials /*world x 32*/, const uint8_t* flags /*world x 3*/, int world,
+                       uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SNARK_H_ */
