@@ -1,0 +1,352 @@
+// C ABI of libb200snark.so (declared in include/b200snark.h): context, key ingest, and the prove orchestration.
+// Host side only — every arithmetic operation runs in the kernels of msm_*.cu / ntt.cu; there is no CPU fallback.
+#include "../../include/b200snark.h"
+#include "internal.hpp"
+#include <cstring>
+#include <cstdio>
+#include <algorithm>
+#include <memory>
+
+using namespace b200;
+
+// ------------------------------------------------------------------------------------------------ ctx plumbing
+void* b200_ctx::scratch(const char* name, size_t bytes) {
+    Slot& s = slots[name];
+    if (s.cap < bytes) {
+        if (s.p) { cudaStreamSynchronize(stream); cudaFree(s.p); s.p = nullptr; s.cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&s.p, want);
+        if (e != cudaSuccess) {
+            e = cudaMalloc(&s.p, bytes);
+            want = bytes;
+        }
+        if (e != cudaSuccess) {
+            s.p = nullptr;
+            (void)cudaGetLastError();   // clear the sticky-free allocation error
+            throw std::runtime_error(std::string("cudaMalloc(") + name + ", " + std::to_string(bytes) + " B): " + cudaGetErrorString(e));
+        }
+        s.cap = want;
+    }
+    return s.p;
+}
+void b200_ctx::t_begin(const char* name) {
+    if (!timing_enabled) return;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a, stream);
+    timing_events.push_back({name, {a, b}});
+}
+void b200_ctx::t_end() {
+    if (!timing_enabled) return;
+    // close the most recent event pair that has not been closed yet (phases nest like a stack)
+    for (size_t i = timing_events.size(); i-- > 0;) {
+        if (timing_events[i].first.empty() || timing_events[i].first[0] != '#') {
+            cudaEventRecord(timing_events[i].second.second, stream);
+            timing_events[i].first = "#" + timing_events[i].first;
+            return;
+        }
+    }
+}
+void b200_ctx::t_collect() {
+    timings.clear();
+    for (auto& ev : timing_events) {
+        float ms = 0.f;
+        if (!ev.first.empty() && ev.first[0] == '#') cudaEventElapsedTime(&ms, ev.second.first, ev.second.second);
+        timings.push_back({ev.first.empty() ? ev.first : ev.first.substr(ev.first[0] == '#' ? 1 : 0), ms});
+        cudaEventDestroy(ev.second.first); cudaEventDestroy(ev.second.second);
+    }
+    timing_events.clear();
+}
+
+namespace {
+
+struct Guard {   // turns C++ exceptions into status codes at the ABI boundary
+    b200_ctx* ctx;
+    template <typename F>
+    int run(F&& f) {
+        try {
+            if (ctx) B200_CUDA_CHECK(cudaSetDevice(ctx->device));
+            return f();
+        } catch (const std::invalid_argument& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_ARG;
+        } catch (const std::domain_error& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_FORMAT;
+        } catch (const std::exception& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_CUDA;
+        }
+    }
+};
+
+struct DevBuf {   // RAII device allocation
+    void* p = nullptr;
+    explicit DevBuf(size_t bytes) { B200_CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(bytes, 16))); }
+    ~DevBuf() { cudaFree(p); }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+inline size_t aff_bytes(int group) { return group == 1 ? 64 : 128; }
+inline size_t xyzz_bytes(int group) { return group == 1 ? 128 : 256; }
+inline size_t aff_limbs(int group) { return group == 1 ? 8 : 16; }
+
+// host affine points + flags -> device array with (0,0) as the infinity encoding
+void upload_points(b200_ctx* ctx, int group, const uint64_t* xy, const uint8_t* inf, size_t n, void* d_out) {
+    const size_t ab = aff_bytes(group);
+    if (!n) return;
+    if (!inf) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(d_out, xy, n * ab, cudaMemcpyHostToDevice, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        return;
+    }
+    std::vector<uint8_t> tmp(n * ab);
+    memcpy(tmp.data(), xy, n * ab);
+    for (size_t i = 0; i < n; ++i)
+        if (inf[i]) memset(tmp.data() + i * ab, 0, ab);
+    B200_CUDA_CHECK(cudaMemcpy(d_out, tmp.data(), n * ab, cudaMemcpyHostToDevice));
+}
+void download_points(b200_ctx* ctx, int group, const void* d_in, size_t n, uint64_t* xy, uint8_t* inf) {
+    const size_t ab = aff_bytes(group);
+    if (!n) return;
+    B200_CUDA_CHECK(cudaMemcpyAsync(xy, d_in, n * ab, cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    const size_t nl = aff_limbs(group);
+    for (size_t i = 0; i < n; ++i) {
+        uint64_t o = 0;
+        for (size_t l = 0; l < nl; ++l) o |= xy[i * nl + l];
+        if (inf) inf[i] = (o == 0);
+        if (o == 0 && group) {   // canonical output for infinity: (0, 1) in Montgomery form is not needed; keep (0,0)
+        }
+    }
+}
+
+// result of g_finish: affine point followed by a u32 flag
+void fetch_finished(b200_ctx* ctx, int group, const void* d_fin, uint64_t* xy, uint8_t* inf) {
+    uint8_t buf[128 + 16];
+    const size_t ab = aff_bytes(group);
+    B200_CUDA_CHECK(cudaMemcpyAsync(buf, d_fin, ab + 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    memcpy(xy, buf, ab);
+    uint32_t f;
+    memcpy(&f, buf + ab, 4);
+    *inf = (uint8_t)(f != 0);
+}
+
+}  // namespace
+
+struct b200_bases {
+    b200_ctx* ctx = nullptr;
+    int group = 1;
+    size_t n = 0;
+    void* d = nullptr;   // affine Montgomery, (0,0) = infinity
+};
+
+extern "C" {
+
+const char* b200_strerror(int code) {
+    switch (code) {
+        case B200_OK: return "ok";
+        case B200_ERR_CUDA: return "CUDA error (no device, launch or allocation failure)";
+        case B200_ERR_ARG: return "invalid argument";
+        case B200_ERR_FORMAT: return "malformed proving key";
+        case B200_ERR_STATE: return "call not valid in this state (e.g. prove before circuit_load)";
+        default: return "unknown error";
+    }
+}
+
+int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
+    if (!out) return B200_ERR_ARG;
+    *out = nullptr;
+    if (n_devices > 1) return B200_ERR_ARG;
+    int dev = (device_ids && n_devices == 1) ? device_ids[0] : 0;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { (void)cudaGetLastError(); return B200_ERR_CUDA; }
+    if (dev < 0 || dev >= count) return B200_ERR_ARG;
+    if (cudaSetDevice(dev) != cudaSuccess) return B200_ERR_CUDA;
+    b200_ctx* c = new b200_ctx();
+    c->device = dev;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return B200_ERR_CUDA; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    *out = c;
+    return B200_OK;
+}
+void b200_shutdown(b200_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto& kv : ctx->slots) cudaFree(kv.second.p);
+    ctx->t_collect();
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+const char* b200_last_error(b200_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+void* b200_stream(b200_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+unsigned long long b200_launch_count(b200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int b200_set_option(b200_ctx* ctx, const char* name, long value) {
+    if (!ctx || !name) return B200_ERR_ARG;
+    if (!strcmp(name, "window")) ctx->window_override = (int)value;
+    else if (!strcmp(name, "chunk")) ctx->chunk_override = (int)value;
+    else if (!strcmp(name, "timing")) ctx->timing_enabled = value != 0;
+    else return B200_ERR_ARG;
+    return B200_OK;
+}
+int b200_timing_count(b200_ctx* ctx) { return ctx ? (int)ctx->timings.size() : 0; }
+int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms) {
+    if (!ctx || i < 0 || i >= (int)ctx->timings.size()) return B200_ERR_ARG;
+    if (name && cap) { strncpy(name, ctx->timings[i].first.c_str(), cap - 1); name[cap - 1] = 0; }
+    if (ms) *ms = ctx->timings[i].second;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ sub-operations
+int b200_field_op(b200_ctx* ctx, int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
+    if (!ctx || !a || !out || field < 0 || field > 1 || op < 0 || op > 7) return B200_ERR_ARG;
+    if ((op <= 2) && !b) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        DevBuf da(n * 32), db(n * 32), dout(n * 32);
+        B200_CUDA_CHECK(cudaMemcpyAsync(da.p, a, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+        if (b) B200_CUDA_CHECK(cudaMemcpyAsync(db.p, b, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+        field_op(ctx, field, op, da.p, db.p, dout.p, n);
+        B200_CUDA_CHECK(cudaMemcpyAsync(out, dout.p, n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        return (int)B200_OK;
+    });
+}
+
+static int group_add(b200_ctx* ctx, int group, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf,
+                     uint64_t* out_xy, uint8_t* out_inf, size_t n) {
+    if (!ctx || !a_xy || !b_xy || !out_xy) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        const size_t ab = aff_bytes(group);
+        DevBuf da(n * ab), db(n * ab), dout(n * ab);
+        upload_points(ctx, group, a_xy, a_inf, n, da.p);
+        upload_points(ctx, group, b_xy, b_inf, n, db.p);
+        g_add_affine(ctx, group, da.p, db.p, dout.p, n);
+        download_points(ctx, group, dout.p, n, out_xy, out_inf);
+        return (int)B200_OK;
+    });
+}
+int b200_g1_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf, uint64_t* out_xy,
+                uint8_t* out_inf, size_t n) {
+    return group_add(ctx, 1, a_xy, a_inf, b_xy, b_inf, out_xy, out_inf, n);
+}
+int b200_g2_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf, uint64_t* out_xy,
+                uint8_t* out_inf, size_t n) {
+    return group_add(ctx, 2, a_xy, a_inf, b_xy, b_inf, out_xy, out_inf, n);
+}
+
+static int fixed_base(b200_ctx* ctx, int group, const uint64_t* scalars, size_t n, uint64_t* out_xy, uint8_t* out_inf) {
+    if (!ctx || !scalars || !out_xy) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        DevBuf ds(n * 32), dout(n * aff_bytes(group));
+        B200_CUDA_CHECK(cudaMemcpyAsync(ds.p, scalars, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+        g_fixed_base(ctx, group, ds.p, n, dout.p);
+        download_points(ctx, group, dout.p, n, out_xy, out_inf);
+        return (int)B200_OK;
+    });
+}
+int b200_g1_fixed_base(b200_ctx* ctx, const uint64_t* s, size_t n, uint64_t* out_xy, uint8_t* out_inf) { return fixed_base(ctx, 1, s, n, out_xy, out_inf); }
+int b200_g2_fixed_base(b200_ctx* ctx, const uint64_t* s, size_t n, uint64_t* out_xy, uint8_t* out_inf) { return fixed_base(ctx, 2, s, n, out_xy, out_inf); }
+
+int b200_ntt(b200_ctx* ctx, uint64_t* data, uint32_t log_m, int mode) {
+    if (!ctx || !data || mode < 0 || mode > 3 || log_m > 28) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        const size_t m = (size_t)1 << log_m;
+        Domain dom;
+        domain_create(ctx, log_m, &dom);
+        std::shared_ptr<Domain> guard(&dom, [](Domain* d) { domain_free(d); });
+        DevBuf d(m * 32);
+        B200_CUDA_CHECK(cudaMemcpyAsync(d.p, data, m * 32, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->t_begin("ntt");
+        ntt_natural(ctx, dom, d.p, mode);
+        ctx->t_end();
+        B200_CUDA_CHECK(cudaMemcpyAsync(data, d.p, m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+// ------------------------------------------------------------------------------------------------ base sets + MSM
+int b200_bases_upload(b200_ctx* ctx, int group, const uint64_t* xy, const uint8_t* inf, size_t n, b200_bases** out) {
+    if (!ctx || !out || (group != 1 && group != 2) || (n && !xy)) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        std::unique_ptr<b200_bases> b(new b200_bases());
+        b->ctx = ctx; b->group = group; b->n = n;
+        B200_CUDA_CHECK(cudaMalloc(&b->d, std::max<size_t>(n * aff_bytes(group), 16)));
+        try { upload_points(ctx, group, xy, inf, n, b->d); } catch (...) { cudaFree(b->d); throw; }
+        *out = b.release();
+        return (int)B200_OK;
+    });
+}
+int b200_bases_generate(b200_ctx* ctx, int group, const uint64_t* scalars, size_t n, b200_bases** out) {
+    if (!ctx || !out || (group != 1 && group != 2) || (n && !scalars)) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        std::unique_ptr<b200_bases> b(new b200_bases());
+        b->ctx = ctx; b->group = group; b->n = n;
+        DevBuf ds(n * 32);
+        B200_CUDA_CHECK(cudaMemcpyAsync(ds.p, scalars, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+        B200_CUDA_CHECK(cudaMalloc(&b->d, std::max<size_t>(n * aff_bytes(group), 16)));
+        try {
+            g_fixed_base(ctx, group, ds.p, n, b->d);
+            B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        } catch (...) { cudaFree(b->d); throw; }
+        *out = b.release();
+        return (int)B200_OK;
+    });
+}
+int b200_bases_download(b200_bases* b, uint64_t* xy, uint8_t* inf) {
+    if (!b || !xy) return B200_ERR_ARG;
+    return Guard{b->ctx}.run([&] { download_points(b->ctx, b->group, b->d, b->n, xy, inf); return (int)B200_OK; });
+}
+size_t b200_bases_count(b200_bases* b) { return b ? b->n : 0; }
+void b200_bases_free(b200_bases* b) {
+    if (!b) return;
+    cudaSetDevice(b->ctx->device);
+    cudaStreamSynchronize(b->ctx->stream);
+    cudaFree(b->d);
+    delete b;
+}
+
+int b200_msm(b200_ctx* ctx, b200_bases* bases, const uint64_t* scalars, size_t n, int on_device, uint64_t* out_xy, uint8_t* out_inf) {
+    if (!ctx || !bases || !out_xy || !out_inf || n > bases->n || (n && !scalars)) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        const int g = bases->group;
+        const void* d_scalars = scalars;
+        ctx->t_begin("msm.total");
+        if (!on_device) {
+            void* ds = ctx->scratch("msm_scalars_in", n * 32);
+            B200_CUDA_CHECK(cudaMemcpyAsync(ds, scalars, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+            d_scalars = ds;
+        }
+        void* acc = ctx->scratch("msm_result", xyzz_bytes(g) + 256);
+        void* fin = (char*)acc + xyzz_bytes(g);
+        msm_run(ctx, g, bases->d, d_scalars, nullptr, n, true, acc);
+        g_finish(ctx, g, acc, 1, nullptr, 0, fin, false);
+        ctx->t_end();
+        fetch_finished(ctx, g, fin, out_xy, out_inf);
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+static int msm_host(b200_ctx* ctx, int group, const uint64_t* bases_xy, const uint8_t* inf, const uint64_t* scalars, size_t n,
+                    uint64_t* out_xy, uint8_t* out_inf) {
+    b200_bases* b = nullptr;
+    int rc = b200_bases_upload(ctx, group, bases_xy, inf, n, &b);
+    if (rc) return rc;
+    rc = b200_msm(ctx, b, scalars, n, 0, out_xy, out_inf);
+    b200_bases_free(b);
+    return rc;
+}
+int b200_msm_g1(b200_ctx* ctx, const uint64_t* bases_xy, const uint8_t* inf, const uint64_t* scalars, size_t n, uint64_t out_xy[8], uint8_t* out_inf) {
+    return msm_host(ctx, 1, bases_xy, inf, scalars, n, out_xy, out_inf);
+}
+int b200_msm_g2(b200_ctx* ctx, const uint64_t* bases_xy, const uint8_t* inf, const uint64_t* scalars, size_t n, uint64_t out_xy[16], uint8_t* out_inf) {
+    return msm_host(ctx, 2, bases_xy, inf, scalars, n, out_xy, out_inf);
+}
+
+}  // extern "C"

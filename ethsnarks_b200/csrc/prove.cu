@@ -1,0 +1,538 @@
+// Proving-key ingest and the Groth16 prove orchestration (C ABI part 2; see include/b200snark.h for the reference map).
+//   key layout parsed here:   /root/reference/src/r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.tcc:54-87,109-143,
+//                             LS/common/data_structures/sparse_vector.tcc:273-322,
+//                             FF/algebra/curves/mcl_bn128/mcl_bn128_g1.cpp:181-295 (mcl points),
+//                             FF/algebra/curves/alt_bn128/alt_bn128_g1.cpp:404-465 (libff points)
+//   prover:                   …zok.tcc:451-550 (no-ZK) and LS/zk_proof_systems/ppzksnark/r1cs_gg_ppzksnark/r1cs_gg_ppzksnark.tcc:485-493 (r,s)
+#include "../../include/b200snark.h"
+#include "internal.hpp"
+#include <cstring>
+#include <algorithm>
+#include <memory>
+
+using namespace b200;
+
+struct b200_bases {   // same definition as in api.cu
+    b200_ctx* ctx;
+    int group;
+    size_t n;
+    void* d;
+};
+
+struct b200_key {
+    b200_ctx* ctx = nullptr;
+    bool full = false;          // has the B query in G1 (r,s mode possible)
+    bool owns_bases = true;
+    int rank = 0, world = 1;
+    uint64_t domain_size = 0;   // num_variables + 1
+    uint64_t nA = 0, nB = 0, nH = 0, nL = 0;   // entries held by this rank
+    uint64_t L_lo = 0;          // first L entry held by this rank (scalar offset)
+    uint64_t H_lo = 0;          // first (bit-reversed) H position held by this rank
+    void *A = nullptr, *B2 = nullptr, *B1 = nullptr, *H = nullptr, *L = nullptr;
+    uint32_t *A_idx = nullptr, *B_idx = nullptr;
+    bool H_bitrev = false;      // H bases stored in bit-reversed order (needs the domain size: set at circuit_load)
+    std::vector<uint8_t> H_host;   // natural-order H bases kept on the host until the domain size is known
+    void* consts_g1 = nullptr;  // alpha_g1, beta_g1, delta_g1 (affine Montgomery)
+    void* consts_g2 = nullptr;  // beta_g2, delta_g2
+    // circuit
+    bool has_circuit = false;
+    uint64_t nc = 0, ni = 0, nv = 0, m = 0;
+    uint32_t logm = 0;
+    DeviceCsr M[3];
+    void* coeffs = nullptr;
+    Domain dom;
+    void *d_w = nullptr, *d_a = nullptr, *d_b = nullptr, *d_c = nullptr;
+    uint64_t H_total = 0;       // |H_query| in the key file
+};
+
+namespace {
+
+struct Guard {
+    b200_ctx* ctx;
+    template <typename F>
+    int run(F&& f) {
+        try {
+            if (ctx) B200_CUDA_CHECK(cudaSetDevice(ctx->device));
+            return f();
+        } catch (const std::invalid_argument& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_ARG;
+        } catch (const std::domain_error& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_FORMAT;
+        } catch (const std::logic_error& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_STATE;
+        } catch (const std::exception& e) {
+            if (ctx) ctx->last_error = e.what();
+            return B200_ERR_CUDA;
+        }
+    }
+};
+
+// ---- byte-stream reader for the reference's mixed ASCII / binary key file
+struct Reader {
+    const uint8_t* p;
+    const uint8_t* end;
+    bool alt;
+    void need(size_t n) const { if ((size_t)(end - p) < n) throw std::domain_error("proving key: unexpected end of data"); }
+    uint64_t number() {   // ASCII decimal terminated by '\n'
+        uint64_t v = 0; bool any = false;
+        while (p < end && *p >= '0' && *p <= '9') { v = v * 10 + (*p - '0'); ++p; any = true; }
+        if (!any || p >= end || *p != '\n') throw std::domain_error("proving key: expected a decimal count followed by newline");
+        ++p;
+        return v;
+    }
+    // reads one point into out (affine Montgomery, zeros for infinity); limbs = 4 per Fq coordinate
+    void point(int group, uint8_t* out) {
+        const size_t ab = group == 1 ? 64 : 128;
+        const size_t raw = alt ? ab : ab + ab / 2;   // mcl stores x,y,z
+        need(1 + raw);
+        const uint8_t flag = *p++;
+        if (flag != '0' && flag != '1') throw std::domain_error("proving key: bad is-zero flag byte");
+        if (flag == '1') memset(out, 0, ab); else memcpy(out, p, ab);
+        p += raw;
+    }
+};
+
+template <typename T>
+T* dev_upload(const std::vector<T>& v) {
+    T* d = nullptr;
+    B200_CUDA_CHECK(cudaMalloc(&d, std::max<size_t>(v.size() * sizeof(T), 16)));
+    if (!v.empty()) B200_CUDA_CHECK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return d;
+}
+void* dev_upload_bytes(const uint8_t* src, size_t bytes) {
+    void* d = nullptr;
+    B200_CUDA_CHECK(cudaMalloc(&d, std::max<size_t>(bytes, 16)));
+    if (bytes) B200_CUDA_CHECK(cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice));
+    return d;
+}
+inline void shard_range(uint64_t n, int rank, int world, uint64_t& lo, uint64_t& hi) {
+    lo = n * (uint64_t)rank / (uint64_t)world;
+    hi = n * (uint64_t)(rank + 1) / (uint64_t)world;
+}
+inline uint32_t bitrev32(uint32_t x, uint32_t bits) {
+    uint32_t r = 0;
+    for (uint32_t i = 0; i < bits; ++i) r |= ((x >> i) & 1u) << (bits - 1 - i);
+    return r;
+}
+
+void key_release(b200_key* k) {
+    if (!k) return;
+    if (k->owns_bases) { cudaFree(k->A); cudaFree(k->B2); cudaFree(k->B1); cudaFree(k->L); }
+    cudaFree(k->H);
+    cudaFree(k->A_idx); cudaFree(k->B_idx); cudaFree(k->consts_g1); cudaFree(k->consts_g2);
+    for (int i = 0; i < 3; ++i) csr_free(&k->M[i]);
+    cudaFree(k->coeffs);
+    if (k->has_circuit) domain_free(&k->dom);
+    cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
+    delete k;
+}
+
+// place this rank's slice of the H bases on the device in bit-reversed order (position p holds H_query[bitrev(p)];
+// the coefficient m-1, which the reference never multiplies, maps to the point at infinity)
+void place_h(b200_key* k) {
+    const uint64_t m = k->m;
+    uint64_t lo, hi;
+    shard_range(m, k->rank, k->world, lo, hi);
+    std::vector<uint8_t> buf((hi - lo) * 64, 0);
+    const uint64_t have = k->H_host.size() / 64;
+    for (uint64_t p = lo; p < hi; ++p) {
+        const uint64_t i = bitrev32((uint32_t)p, k->logm);
+        if (i < have && i + 1 < m) memcpy(&buf[(p - lo) * 64], &k->H_host[i * 64], 64);
+    }
+    cudaFree(k->H);
+    k->H = dev_upload_bytes(buf.data(), buf.size());
+    k->H_lo = lo; k->nH = hi - lo;
+    k->H_bitrev = true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt, int rank, int world, b200_key** out) {
+    if (!ctx || !bytes || !out || fmt < 0 || fmt > 3 || world < 1 || rank < 0 || rank >= world) return B200_ERR_ARG;
+    *out = nullptr;
+    return Guard{ctx}.run([&] {
+        std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
+        k->ctx = ctx; k->rank = rank; k->world = world;
+        k->full = (fmt & 1);
+        Reader rd{(const uint8_t*)bytes, (const uint8_t*)bytes + len, fmt >= 2};
+        uint8_t c1[3 * 64], c2[2 * 128];
+        rd.point(1, c1);            // alpha_g1
+        rd.point(1, c1 + 64);       // beta_g1
+        rd.point(2, c2);            // beta_g2
+        rd.point(1, c1 + 128);      // delta_g1
+        rd.point(2, c2 + 128);      // delta_g2
+        k->consts_g1 = dev_upload_bytes(c1, sizeof c1);
+        k->consts_g2 = dev_upload_bytes(c2, sizeof c2);
+        // A query: sparse_vector<G1>
+        k->domain_size = rd.number();
+        auto read_sparse = [&](bool is_b, std::vector<uint32_t>& idx, std::vector<uint8_t>& v1, std::vector<uint8_t>& v2) {
+            const uint64_t n_idx = rd.number();
+            std::vector<uint64_t> all_idx(n_idx);
+            for (uint64_t i = 0; i < n_idx; ++i) all_idx[i] = rd.number();
+            const uint64_t n_val = rd.number();
+            if (n_val != n_idx) throw std::domain_error("proving key: sparse vector with different index and value counts");
+            // kc_multiexp.tcc:54-84 — entries from the first index >= scalar_size on are ignored
+            uint64_t n_use = n_idx;
+            for (uint64_t i = 0; i < n_idx; ++i) if (all_idx[i] >= k->domain_size) { n_use = i; break; }
+            uint64_t lo, hi;
+            shard_range(n_use, rank, world, lo, hi);
+            idx.resize(hi - lo);
+            if (is_b) v2.resize((hi - lo) * 128);
+            if (!is_b || k->full) v1.resize((hi - lo) * 64);
+            uint8_t scratch[128];
+            for (uint64_t i = 0; i < n_val; ++i) {
+                const bool keep = (i >= lo && i < hi);
+                if (is_b) {
+                    rd.point(2, keep ? &v2[(i - lo) * 128] : scratch);
+                    if (k->full) rd.point(1, keep ? &v1[(i - lo) * 64] : scratch);
+                } else {
+                    rd.point(1, keep ? &v1[(i - lo) * 64] : scratch);
+                }
+                if (keep) idx[i - lo] = (uint32_t)all_idx[i];
+            }
+        };
+        {
+            std::vector<uint32_t> idx; std::vector<uint8_t> v1, v2;
+            read_sparse(false, idx, v1, v2);
+            k->nA = idx.size();
+            k->A_idx = dev_upload(idx);
+            k->A = dev_upload_bytes(v1.data(), v1.size());
+        }
+        {
+            const uint64_t dsB = rd.number();
+            if (dsB != k->domain_size) throw std::domain_error("proving key: A and B query domain sizes differ");
+            std::vector<uint32_t> idx; std::vector<uint8_t> v1, v2;
+            read_sparse(true, idx, v1, v2);
+            k->nB = idx.size();
+            k->B_idx = dev_upload(idx);
+            k->B2 = dev_upload_bytes(v2.data(), v2.size());
+            if (k->full) k->B1 = dev_upload_bytes(v1.data(), v1.size());
+        }
+        {   // H query: kept on the host until circuit_load fixes the domain (bit-reversed placement)
+            const uint64_t n = rd.number();
+            k->H_total = n;
+            k->H_host.resize(n * 64);
+            for (uint64_t i = 0; i < n; ++i) rd.point(1, &k->H_host[i * 64]);
+        }
+        {
+            const uint64_t n = rd.number();
+            uint64_t lo, hi;
+            shard_range(n, rank, world, lo, hi);
+            std::vector<uint8_t> v((hi - lo) * 64);
+            uint8_t scratch[64];
+            for (uint64_t i = 0; i < n; ++i) rd.point(1, (i >= lo && i < hi) ? &v[(i - lo) * 64] : scratch);
+            k->L = dev_upload_bytes(v.data(), v.size());
+            k->nL = hi - lo; k->L_lo = lo;
+        }
+        *out = k.release();
+        return (int)B200_OK;
+    });
+}
+int b200_key_load(b200_ctx* ctx, const void* bytes, size_t len, int fmt, b200_key** out) {
+    return b200_key_load_sharded(ctx, bytes, len, fmt, 0, 1, out);
+}
+
+int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b200_bases* B_g2, b200_bases* B_g1, const uint32_t* B_idx,
+                        b200_bases* H, b200_bases* L, const uint64_t* g1c, const uint64_t* g2c, uint64_t num_variables, uint64_t num_inputs,
+                        b200_key** out) {
+    if (!ctx || !A || !B_g2 || !H || !L || !g1c || !g2c || !out) return B200_ERR_ARG;
+    if (A->group != 1 || B_g2->group != 2 || H->group != 1 || L->group != 1 || (B_g1 && (B_g1->group != 1 || B_g1->n != B_g2->n))) return B200_ERR_ARG;
+    if (L->n != num_variables - num_inputs) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
+        k->ctx = ctx; k->owns_bases = false; k->full = B_g1 != nullptr;
+        k->domain_size = num_variables + 1;
+        k->A = A->d; k->nA = A->n; k->B2 = B_g2->d; k->nB = B_g2->n; k->B1 = B_g1 ? B_g1->d : nullptr;
+        k->L = L->d; k->nL = L->n;
+        auto idx_or_identity = [&](const uint32_t* idx, size_t n) {
+            std::vector<uint32_t> v(n);
+            for (size_t i = 0; i < n; ++i) {
+                v[i] = idx ? idx[i] : (uint32_t)i;
+                if (v[i] > num_variables) throw std::invalid_argument("key_from_bases: query index beyond num_variables");
+            }
+            return dev_upload(v);
+        };
+        k->A_idx = idx_or_identity(A_idx, A->n);
+        k->B_idx = idx_or_identity(B_idx, B_g2->n);
+        k->consts_g1 = dev_upload_bytes((const uint8_t*)g1c, 3 * 64);
+        k->consts_g2 = dev_upload_bytes((const uint8_t*)g2c, 2 * 128);
+        k->H_total = H->n;
+        k->H_host.resize(H->n * 64);
+        if (H->n) B200_CUDA_CHECK(cudaMemcpy(k->H_host.data(), H->d, H->n * 64, cudaMemcpyDeviceToHost));
+        *out = k.release();
+        return (int)B200_OK;
+    });
+}
+
+void b200_key_free(b200_key* key) {
+    if (!key) return;
+    cudaSetDevice(key->ctx->device);
+    cudaStreamSynchronize(key->ctx->stream);
+    key_release(key);
+}
+int b200_key_info(b200_key* k, uint64_t out[8]) {
+    if (!k || !out) return B200_ERR_ARG;
+    out[0] = k->domain_size; out[1] = k->nA; out[2] = k->nB; out[3] = k->H_bitrev ? k->nH : k->H_total; out[4] = k->nL;
+    out[5] = k->full; out[6] = k->m; out[7] = k->ni;
+    return B200_OK;
+}
+
+int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b200_csr* C, const uint64_t* coeffs, size_t n_coeffs,
+                      uint32_t num_inputs, uint64_t num_variables) {
+    if (!k || !A || !B || !C || !coeffs || !n_coeffs) return B200_ERR_ARG;
+    if (A->n_rows != B->n_rows || A->n_rows != C->n_rows) return B200_ERR_ARG;
+    if (num_variables + 1 != k->domain_size || num_inputs > num_variables) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    return Guard{ctx}.run([&] {
+        const b200_csr* mats[3] = {A, B, C};
+        for (int i = 0; i < 3; ++i) {
+            const uint64_t nnz = mats[i]->n_rows ? mats[i]->row_ptr[mats[i]->n_rows] : 0;
+            for (uint64_t j = 0; j < nnz; ++j) {
+                if (mats[i]->col[j] > num_variables) throw std::invalid_argument("circuit_load: variable index out of range");
+                if (mats[i]->coeff_idx[j] >= n_coeffs) throw std::invalid_argument("circuit_load: coefficient index out of range");
+            }
+        }
+        if (k->has_circuit) {
+            for (int i = 0; i < 3; ++i) csr_free(&k->M[i]);
+            cudaFree(k->coeffs); k->coeffs = nullptr;
+            domain_free(&k->dom);
+            cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
+            k->d_w = k->d_a = k->d_b = k->d_c = nullptr;
+            k->has_circuit = false;
+        }
+        k->nc = A->n_rows; k->ni = num_inputs; k->nv = num_variables;
+        // get_domain (src/stubs.cpp:61-75): m = roundUpToNearestPowerOf2(num_constraints + num_inputs + 1)
+        uint64_t need = k->nc + k->ni + 1;
+        uint32_t logm = 0;
+        while (((uint64_t)1 << logm) < need) ++logm;
+        if (logm < 1) logm = 1;
+        k->logm = logm; k->m = (uint64_t)1 << logm;
+        if (k->H_total + 1 < k->m) throw std::invalid_argument("circuit_load: H query shorter than domain size - 1");
+        for (int i = 0; i < 3; ++i) csr_upload(ctx, mats[i]->row_ptr, mats[i]->col, mats[i]->coeff_idx, mats[i]->n_rows, &k->M[i]);
+        k->coeffs = dev_upload_bytes((const uint8_t*)coeffs, n_coeffs * 32);
+        domain_create(ctx, logm, &k->dom);
+        k->has_circuit = true;
+        B200_CUDA_CHECK(cudaMalloc(&k->d_w, (k->nv + 1) * 32));
+        B200_CUDA_CHECK(cudaMalloc(&k->d_a, k->m * 32));
+        B200_CUDA_CHECK(cudaMalloc(&k->d_b, k->m * 32));
+        B200_CUDA_CHECK(cudaMalloc(&k->d_c, k->m * 32));
+        place_h(k);
+        return (int)B200_OK;
+    });
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------ prove
+namespace {
+
+void run_witness_eval(b200_key* k, const uint64_t* witness) {
+    b200_ctx* ctx = k->ctx;
+    ctx->t_begin("h2d.witness");
+    B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->t_end();
+    ctx->t_begin("witness_eval");
+    spmv(ctx, k->M[0], k->coeffs, k->d_w, k->d_a);
+    spmv(ctx, k->M[1], k->coeffs, k->d_w, k->d_b);
+    spmv(ctx, k->M[2], k->coeffs, k->d_w, k->d_c);
+    witness_rows(ctx, k->d_w, k->d_a, k->d_b, k->d_c, k->nc, k->ni, k->m);
+    ctx->t_end();
+}
+void run_h(b200_key* k) {
+    b200_ctx* ctx = k->ctx;
+    ctx->t_begin("h_chain");
+    h_chain(ctx, k->dom, k->d_a, k->d_b, k->d_c);
+    ctx->t_end();
+}
+// the four (five) MSMs over this rank's key slice; results as XYZZ in acc[0..4]: A, B(G2), H, L, B(G1)
+struct Acc { void *A, *B2, *H, *L, *B1, *tmp, *fin; };
+Acc acc_slots(b200_ctx* ctx) {
+    char* base = (char*)ctx->scratch("prove_acc", 8192);
+    Acc a;
+    a.A = base; a.H = base + 128; a.L = base + 256; a.B1 = base + 384; a.B2 = base + 512; a.tmp = base + 768; a.fin = base + 4096;
+    return a;
+}
+void run_msms(b200_key* k, const Acc& a, bool want_b1) {
+    b200_ctx* ctx = k->ctx;
+    ctx->t_begin("msm.A");
+    msm_run(ctx, 1, k->A, k->d_w, k->A_idx, k->nA, true, a.A);
+    ctx->t_end();
+    ctx->t_begin("msm.B_g2");
+    msm_run(ctx, 2, k->B2, k->d_w, k->B_idx, k->nB, true, a.B2);
+    ctx->t_end();
+    ctx->t_begin("msm.H");
+    msm_run(ctx, 1, k->H, (const char*)k->d_c + k->H_lo * 32, nullptr, k->nH, true, a.H);
+    ctx->t_end();
+    ctx->t_begin("msm.L");
+    msm_run(ctx, 1, k->L, (const char*)k->d_w + (k->ni + 1 + k->L_lo) * 32, nullptr, k->nL, true, a.L);
+    ctx->t_end();
+    if (want_b1) {
+        ctx->t_begin("msm.B_g1");
+        msm_run(ctx, 1, k->B1, k->d_w, k->B_idx, k->nB, true, a.B1);
+        ctx->t_end();
+    }
+}
+void fetch(b200_ctx* ctx, int group, const void* d_fin, uint64_t* xy, uint8_t* inf) {
+    uint8_t buf[128 + 16];
+    const size_t ab = group == 1 ? 64 : 128;
+    B200_CUDA_CHECK(cudaMemcpyAsync(buf, d_fin, ab + 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    memcpy(xy, buf, ab);
+    uint32_t f;
+    memcpy(&f, buf + ab, 4);
+    *inf = (uint8_t)(f != 0);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_witness_eval(b200_key* k, const uint64_t* witness, uint64_t* a_out, uint64_t* b_out, uint64_t* c_out) {
+    if (!k || !witness || !a_out || !b_out || !c_out) return B200_ERR_ARG;
+    if (!k->has_circuit) { k->ctx->last_error = "witness_eval before circuit_load"; return B200_ERR_STATE; }
+    b200_ctx* ctx = k->ctx;
+    return Guard{ctx}.run([&] {
+        run_witness_eval(k, witness);
+        B200_CUDA_CHECK(cudaMemcpyAsync(a_out, k->d_a, k->m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaMemcpyAsync(b_out, k->d_b, k->m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaMemcpyAsync(c_out, k->d_c, k->m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+int b200_h(b200_key* k, const uint64_t* witness, uint64_t* h_out) {
+    if (!k || !witness || !h_out) return B200_ERR_ARG;
+    if (!k->has_circuit) { k->ctx->last_error = "h before circuit_load"; return B200_ERR_STATE; }
+    b200_ctx* ctx = k->ctx;
+    return Guard{ctx}.run([&] {
+        run_witness_eval(k, witness);
+        run_h(k);
+        bitrev_permute(ctx, k->d_c, k->d_a, k->logm, 32);   // bit-reversed -> natural order for the caller
+        B200_CUDA_CHECK(cudaMemcpyAsync(h_out, k->d_a, k->m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const uint64_t s[4], uint64_t A_xy[8], uint64_t B_xy[16],
+               uint64_t C_xy[8], uint8_t flags[3]) {
+    if (!k || !witness || !A_xy || !B_xy || !C_xy || !flags || ((r == nullptr) != (s == nullptr))) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (!k->has_circuit) { ctx->last_error = "prove before circuit_load"; return B200_ERR_STATE; }
+    if (k->world != 1) { ctx->last_error = "prove on a sharded key: use prove_partial + proof_combine"; return B200_ERR_STATE; }
+    if (r && !k->full) { ctx->last_error = "r,s proving needs a FULL key (B query in G1)"; return B200_ERR_STATE; }
+    return Guard{ctx}.run([&] {
+        ctx->t_begin("prove.total");
+        run_witness_eval(k, witness);
+        run_h(k);
+        Acc a = acc_slots(ctx);
+        run_msms(k, a, r != nullptr);
+        ctx->t_begin("finish");
+        char* fin = (char*)a.fin;
+        const char* c1 = (const char*)k->consts_g1;   // alpha, beta, delta (64 B each)
+        const char* c2 = (const char*)k->consts_g2;   // beta, delta (128 B each)
+        if (!r) {
+            g_finish(ctx, 1, a.A, 1, c1, 1, fin, true);                  // g_A = alpha_g1 + evaluation_At
+            g_finish(ctx, 2, a.B2, 1, c2, 1, fin + 256, true);           // g_B = beta_g2 + evaluation_Bt
+            g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, true);       // g_C = evaluation_Ht + evaluation_Lt (H, L adjacent)
+        } else {
+            // scalars r, s, -(r s) on the device
+            char* sc = (char*)ctx->scratch("prove_rs", 4 * 32);
+            B200_CUDA_CHECK(cudaMemcpyAsync(sc, r, 32, cudaMemcpyHostToDevice, ctx->stream));
+            B200_CUDA_CHECK(cudaMemcpyAsync(sc + 32, s, 32, cudaMemcpyHostToDevice, ctx->stream));
+            field_op(ctx, 0, B200_OP_MUL, sc, sc + 32, sc + 64, 1);
+            field_op(ctx, 0, B200_OP_NEG, sc + 64, nullptr, sc + 96, 1);
+            char* t = (char*)a.tmp;   // XYZZ temporaries, 256 B apart
+            // g1_A = alpha + sum A + r delta1   (Montgomery affine kept for the s*g1_A term)
+            g_scalar_mul(ctx, 1, c1 + 128, sc, t);
+            B200_CUDA_CHECK(cudaMemcpyAsync(t + 128, a.A, 128, cudaMemcpyDeviceToDevice, ctx->stream));
+            g_finish(ctx, 1, t, 2, c1, 1, fin + 1024, false);
+            g_finish(ctx, 1, t, 2, c1, 1, fin, true);
+            // g2_B = beta2 + sum B2 + s delta2
+            g_scalar_mul(ctx, 2, c2 + 128, sc + 32, t + 256);
+            B200_CUDA_CHECK(cudaMemcpyAsync(t + 512, a.B2, 256, cudaMemcpyDeviceToDevice, ctx->stream));
+            g_finish(ctx, 2, t + 256, 2, c2, 1, fin + 256, true);
+            // g1_B = beta1 + sum B1 + s delta1
+            g_scalar_mul(ctx, 1, c1 + 128, sc + 32, t);
+            B200_CUDA_CHECK(cudaMemcpyAsync(t + 128, a.B1, 128, cudaMemcpyDeviceToDevice, ctx->stream));
+            g_finish(ctx, 1, t, 2, c1 + 64, 1, fin + 1280, false);
+            // g1_C = sum H + sum L + s g1_A + r g1_B - r s delta1
+            char* u = t + 768;
+            B200_CUDA_CHECK(cudaMemcpyAsync(u, a.H, 256, cudaMemcpyDeviceToDevice, ctx->stream));   // H and L
+            g_scalar_mul(ctx, 1, fin + 1024, sc + 32, u + 256);
+            g_scalar_mul(ctx, 1, fin + 1280, sc, u + 384);
+            g_scalar_mul(ctx, 1, c1 + 128, sc + 96, u + 512);
+            g_finish(ctx, 1, u, 5, nullptr, 0, fin + 512, true);
+        }
+        ctx->t_end();
+        ctx->t_end();   // prove.total
+        fetch(ctx, 1, fin, A_xy, &flags[0]);
+        fetch(ctx, 2, fin + 256, B_xy, &flags[1]);
+        fetch(ctx, 1, fin + 512, C_xy, &flags[2]);
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+int b200_prove_partial(b200_key* k, const uint64_t* witness, uint64_t partial[32], uint8_t flags[3]) {
+    if (!k || !witness || !partial || !flags) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (!k->has_circuit) { ctx->last_error = "prove_partial before circuit_load"; return B200_ERR_STATE; }
+    return Guard{ctx}.run([&] {
+        ctx->t_begin("prove.total");
+        run_witness_eval(k, witness);
+        run_h(k);
+        Acc a = acc_slots(ctx);
+        run_msms(k, a, false);
+        char* fin = (char*)a.fin;
+        g_finish(ctx, 1, a.A, 1, nullptr, 0, fin, false);
+        g_finish(ctx, 2, a.B2, 1, nullptr, 0, fin + 256, false);
+        g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, false);
+        ctx->t_end();
+        fetch(ctx, 1, fin, partial, &flags[0]);
+        fetch(ctx, 2, fin + 256, partial + 8, &flags[1]);
+        fetch(ctx, 1, fin + 512, partial + 24, &flags[2]);
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+int b200_proof_combine(b200_key* k, const uint64_t* partials, const uint8_t* pflags, int world, uint64_t A_xy[8], uint64_t B_xy[16],
+                       uint64_t C_xy[8], uint8_t flags[3]) {
+    if (!k || !partials || !pflags || world < 1 || !A_xy || !B_xy || !C_xy || !flags) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    return Guard{ctx}.run([&] {
+        std::vector<uint8_t> a1((size_t)(world + 1) * 64, 0), b2((size_t)(world + 1) * 128, 0), c1((size_t)world * 64, 0);
+        for (int i = 0; i < world; ++i) {
+            const uint64_t* p = partials + (size_t)i * 32;
+            if (!pflags[i * 3 + 0]) memcpy(&a1[(size_t)i * 64], p, 64);
+            if (!pflags[i * 3 + 1]) memcpy(&b2[(size_t)i * 128], p + 8, 128);
+            if (!pflags[i * 3 + 2]) memcpy(&c1[(size_t)i * 64], p + 24, 64);
+        }
+        char* buf = (char*)ctx->scratch("combine", (size_t)(world + 1) * 256 + 1024);
+        char* fin = buf + (size_t)(world + 1) * 256;
+        // alpha_g1 / beta_g2 are appended as one more affine term
+        B200_CUDA_CHECK(cudaMemcpyAsync(buf, a1.data(), (size_t)world * 64, cudaMemcpyHostToDevice, ctx->stream));
+        B200_CUDA_CHECK(cudaMemcpyAsync(buf + (size_t)world * 64, k->consts_g1, 64, cudaMemcpyDeviceToDevice, ctx->stream));
+        g_finish(ctx, 1, nullptr, 0, buf, world + 1, fin, true);
+        fetch(ctx, 1, fin, A_xy, &flags[0]);
+        B200_CUDA_CHECK(cudaMemcpyAsync(buf, b2.data(), (size_t)world * 128, cudaMemcpyHostToDevice, ctx->stream));
+        B200_CUDA_CHECK(cudaMemcpyAsync(buf + (size_t)world * 128, k->consts_g2, 128, cudaMemcpyDeviceToDevice, ctx->stream));
+        g_finish(ctx, 2, nullptr, 0, buf, world + 1, fin, true);
+        fetch(ctx, 2, fin, B_xy, &flags[1]);
+        B200_CUDA_CHECK(cudaMemcpyAsync(buf, c1.data(), (size_t)world * 64, cudaMemcpyHostToDevice, ctx->stream));
+        g_finish(ctx, 1, nullptr, 0, buf, world, fin, true);
+        fetch(ctx, 1, fin, C_xy, &flags[2]);
+        return (int)B200_OK;
+    });
+}
+
+}  // extern "C"
