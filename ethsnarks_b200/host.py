@@ -1,0 +1,231 @@
+"""Host-side mirror of the reference's prover entry points, on top of the C ABI (lib.py).
+
+Names, argument meaning and error behaviour follow the reference (paths relative to the reference tree):
+  Config                     src/prover_config.hpp:8-35        (CPU-only knobs are accepted and ignored)
+  ProverContext              src/r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.hpp:279-291
+  load_proving_key           src/stubs.cpp:36-39
+  get_domain                 src/stubs.cpp:49-75               (returns the domain size; the tables live on the device)
+  prove                      src/stubs.cpp:42-47               (returns the proof JSON)
+  proof_to_json              src/export.cpp:99-121
+  Protoboard / R1CS          just enough of libsnark's protoboard (values, primary_input, constraint_system) to carry a
+                             witness and a constraint list into prove(); gadget construction is out of scope
+  generate_r1cs_example_*    depends/libsnark/libsnark/relations/constraint_satisfaction_problems/r1cs/examples/r1cs_examples.tcc:25-161
+"""
+import hashlib
+import struct
+import numpy as np
+from . import lib as _lib
+
+R_MOD = 21888242871839275222246405745257275088548364400416034343698204186575808495617
+Q_MOD = 21888242871839275222246405745257275088696311157297823662689037894645226208583
+MONT_R = 1 << 256
+
+
+def ints_to_limbs(xs):
+    """list of ints (< 2^256) -> (n, 4) uint64 little-endian limbs"""
+    buf = b"".join(int(x).to_bytes(32, "little") for x in xs)
+    return np.frombuffer(buf, dtype=np.uint64).reshape(-1, 4).copy()
+
+
+def limbs_to_ints(a):
+    a = np.ascontiguousarray(a, dtype=np.uint64).reshape(-1, 4)
+    raw = a.tobytes()
+    return [int.from_bytes(raw[i * 32:(i + 1) * 32], "little") for i in range(a.shape[0])]
+
+
+def fr_to_mont(xs):
+    return ints_to_limbs([(x * MONT_R) % R_MOD for x in xs])
+
+
+def fr_from_mont(a):
+    rinv = pow(MONT_R, -1, R_MOD)
+    return [(x * rinv) % R_MOD for x in limbs_to_ints(a)]
+
+
+def sha512_rng(idx, p=R_MOD):
+    """libff::SHA512_rng<FieldT>(idx) (depends/libsnark/depends/libff/libff/common/rng.tcc:25-71)"""
+    it = 0
+    while True:
+        h = hashlib.sha512(struct.pack("<QQ", idx, it)).digest()
+        v = int.from_bytes(h[:32], "little") & ((1 << 254) - 1)
+        if v < p:
+            return v
+        it += 1
+
+
+class Config:
+    """libsnark::Config (src/prover_config.hpp:8-35): same fields, same defaults."""
+
+    def __init__(self):
+        self.num_threads = 1
+        self.smt = False
+        self.fft = "recursive"
+        self.radixes = []
+        self.swapAB = True
+        self.multi_exp_c = 0                 # 0 -> chosen by the backend's cost model (the CPU reference maps 0 -> 16)
+        self.multi_exp_prefetch_locality = 0
+        self.prefetch_stride = 128
+        self.multi_exp_look_ahead = 1
+
+
+class R1CS:
+    """Constraint system as three CSR matrices over a shared coefficient table."""
+
+    def __init__(self, num_inputs, num_variables, A, B, C, coeffs):
+        self.num_inputs, self.num_variables = num_inputs, num_variables
+        self.A, self.B, self.C = A, B, C          # (row_ptr u64, col u32, coeff_idx u32)
+        self.coeffs = list(coeffs)                # ints, standard form
+        self.num_constraints = len(A[0]) - 1
+
+    def is_satisfied(self, values):
+        def row(M, i):
+            rp, col, ci = M
+            return sum(self.coeffs[ci[k]] * values[col[k]] for k in range(int(rp[i]), int(rp[i + 1]))) % R_MOD
+        return all((row(self.A, i) * row(self.B, i) - row(self.C, i)) % R_MOD == 0 for i in range(self.num_constraints))
+
+
+class Protoboard:
+    """values[0] is the constant ONE (LS/gadgetlib1/protoboard.tcc:26-33)."""
+
+    def __init__(self, cs, assignment):
+        self.cs = cs
+        self.values = [1] + [int(v) % R_MOD for v in assignment]
+        assert len(self.values) == cs.num_variables + 1
+
+    def primary_input(self):
+        return self.values[1:1 + self.cs.num_inputs]
+
+    def get_constraint_system(self):
+        return self.cs
+
+    def num_constraints(self):
+        return self.cs.num_constraints
+
+    def num_inputs(self):
+        return self.cs.num_inputs
+
+
+def _csr(rows):
+    rp = np.zeros(len(rows) + 1, dtype=np.uint64)
+    cols, cis = [], []
+    for i, r in enumerate(rows):
+        for (v, c) in r:
+            cols.append(v); cis.append(c)
+        rp[i + 1] = len(cols)
+    return rp, np.array(cols, dtype=np.uint32), np.array(cis, dtype=np.uint32)
+
+
+def generate_r1cs_example_with_field_input(num_constraints, num_inputs, seed_a=0, seed_b=1):
+    """r1cs_examples.tcc:25-93 with a, b = SHA512_rng(seed_a), SHA512_rng(seed_b) instead of random_element()."""
+    assert num_inputs <= num_constraints + 2
+    nv = num_constraints + 2
+    a, b = sha512_rng(seed_a), sha512_rng(seed_b)
+    fa = [a, b]
+    # CSR built directly in numpy-friendly lists (coefficient table = [1])
+    rpA = np.zeros(num_constraints + 1, np.uint64); rpB = np.zeros(num_constraints + 1, np.uint64); rpC = np.zeros(num_constraints + 1, np.uint64)
+    colA, colB, colC = [], [], []
+    for i in range(num_constraints - 1):
+        if i % 2:
+            colA.append(i + 1); colB.append(i + 2); colC.append(i + 3)
+            tmp = a * b % R_MOD
+        else:
+            colB.append(0); colA.append(i + 1); colA.append(i + 2); colC.append(i + 3)
+            tmp = (a + b) % R_MOD
+        fa.append(tmp)
+        a, b = b, tmp
+        rpA[i + 1] = len(colA); rpB[i + 1] = len(colB); rpC[i + 1] = len(colC)
+    fin = sum(fa[:nv - 1]) % R_MOD
+    dense = list(range(1, nv))
+    colA += dense; colB += dense; colC.append(nv)
+    rpA[num_constraints] = len(colA); rpB[num_constraints] = len(colB); rpC[num_constraints] = len(colC)
+    fa.append(fin * fin % R_MOD)
+    mk = lambda rp, col: (rp, np.array(col, dtype=np.uint32), np.zeros(len(col), dtype=np.uint32))
+    cs = R1CS(num_inputs, nv, mk(rpA, colA), mk(rpB, colB), mk(rpC, colC), [1])
+    return Protoboard(cs, fa)
+
+
+def generate_r1cs_example_with_binary_input(num_constraints, num_inputs, seed=1):
+    """r1cs_examples.tcc:96-161 with std::rand replaced by a seeded 64-bit LCG (all witness values are 0/1)."""
+    assert num_inputs >= 1
+    mask = (1 << 64) - 1
+    st = (seed * 6364136223846793005 + 1442695040888963407) & mask
+
+    def rnd():
+        nonlocal st
+        st = (st * 6364136223846793005 + 1442695040888963407) & mask
+        return st >> 33
+    bits = [rnd() % 2 for _ in range(num_inputs)]
+    rowsA, rowsB, rowsC = [], [], []
+    lastvar = num_inputs - 1
+    for i in range(num_constraints):
+        lastvar += 1
+        u = rnd() % num_inputs if i == 0 else rnd() % i
+        v = rnd() % num_inputs if i == 0 else rnd() % i
+        rowsA.append([(u + 1, 2)]); rowsB.append([(v + 1, 0)])
+        rowsC.append(([(u + 1, 2)] if u == v else [(u + 1, 0), (v + 1, 0)]) + [(lastvar + 1, 1)])
+        bits.append(bits[u] ^ bits[v])
+    cs = R1CS(num_inputs, num_inputs + num_constraints, _csr(rowsA), _csr(rowsB), _csr(rowsC), [1, R_MOD - 1, 2, R_MOD - 2])
+    return Protoboard(cs, bits)
+
+
+def _hex(x):
+    return "0x%x" % x
+
+
+def proof_to_json(proof, primary_input):
+    """src/export.cpp:56-121: affine hex, G2 as [x.c1, x.c0], [y.c1, y.c0]; byte-for-byte the reference's layout."""
+    A, B, Cc, inf = proof
+    a = limbs_to_ints(A); b = limbs_to_ints(B); c = limbs_to_ints(Cc)
+    if inf[0]: a = [0, 1]
+    if inf[1]: b = [0, 0, 1, 0]
+    if inf[2]: c = [0, 1]
+    s = "{\n"
+    s += ' "A" :["%s", "%s"],\n' % (_hex(a[0]), _hex(a[1]))
+    s += ' "B"  :[["%s", "%s"],\n ["%s", "%s"]],\n' % (_hex(b[1]), _hex(b[0]), _hex(b[3]), _hex(b[2]))
+    s += ' "C"  :["%s", "%s"],\n' % (_hex(c[0]), _hex(c[1]))
+    s += ' "input" :[' + ", ".join('"%s"' % _hex(v) for v in primary_input) + "]\n"
+    s += "}"
+    return s
+
+
+def load_proving_key(ctx, pk_file_or_bytes, fmt=_lib.FMT_MCL_NOZK, rank=0, world=1):
+    """ethsnarks::load_proving_key (src/stubs.cpp:36-39); a missing file raises like the reference's assert."""
+    if isinstance(pk_file_or_bytes, (bytes, bytearray, memoryview)):
+        data = bytes(pk_file_or_bytes)
+    else:
+        with open(pk_file_or_bytes, "rb") as fh:
+            data = fh.read()
+    return _lib.ProvingKey.load(ctx, data, fmt, rank, world)
+
+
+def get_domain(pb, pk=None, config=None):
+    """src/stubs.cpp:49-75: the domain size roundUpToNearestPowerOf2(num_constraints + num_inputs + 1)."""
+    need = pb.num_constraints() + pb.num_inputs() + 1
+    m = 1
+    while m < need:
+        m *= 2
+    return max(m, 2)
+
+
+class ProverContext:
+    """libsnark::ProverContext (…zok.hpp:279-291): the key, the constraint system, the domain and the scratch buffers
+    that are reused across proofs — here they are device-resident behind the key handle."""
+
+    def __init__(self, proving_key, pb, config=None):
+        self.provingKey = proving_key
+        self.config = config or Config()
+        cs = pb.get_constraint_system()
+        self.constraint_system = cs
+        self.domain = get_domain(pb)
+        if self.config.multi_exp_c:
+            proving_key.ctx.set_option("window", self.config.multi_exp_c)
+        proving_key.load_circuit(cs.A, cs.B, cs.C, fr_to_mont(cs.coeffs), cs.num_inputs, cs.num_variables)
+
+
+def prove(context, pb, r=None, s=None):
+    """ethsnarks::prove (src/stubs.cpp:42-47): witness in, proof JSON out."""
+    w = fr_to_mont(pb.values)
+    rr = fr_to_mont([r])[0] if r is not None else None
+    ss = fr_to_mont([s])[0] if s is not None else None
+    proof = context.provingKey.prove(w, rr, ss)
+    return proof_to_json(proof, pb.primary_input())
