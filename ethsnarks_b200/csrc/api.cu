@@ -201,6 +201,11 @@ int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms) {
     return B200_OK;
 }
 
+int b200_imad_peak(b200_ctx* ctx, int reps, double* macs_per_s) {
+    if (!ctx || !macs_per_s || reps < 1) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] { *macs_per_s = imad_peak(ctx, reps); return (int)B200_OK; });
+}
+
 // ------------------------------------------------------------------------------------------------ sub-operations
 int b200_field_op(b200_ctx* ctx, int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
     if (!ctx || !a || !out || field < 0 || field > 1 || op < 0 || op > 7) return B200_ERR_ARG;

@@ -89,6 +89,7 @@ void ntt_natural(b200_ctx* ctx, const Domain& dom, void* d_data, int mode);
 // coefficients of H in BIT-REVERSED order (c[p] = h[bitrev(p)]), a and b are clobbered.
 void h_chain(b200_ctx* ctx, const Domain& dom, void* d_a, void* d_b, void* d_c);
 void bitrev_permute(b200_ctx* ctx, const void* d_in, void* d_out, uint32_t logm, size_t elem_bytes);
+double imad_peak(b200_ctx* ctx, int reps);   // wide 32x32+64 multiply-adds per second, best of reps
 void field_op(b200_ctx* ctx, int field, int op, const void* d_a, const void* d_b, void* d_out, size_t n);
 
 // --- spmv (in ntt.cu) -----------------------------------------------------------------------------------------

@@ -242,7 +242,7 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
                         b200_key** out) {
     if (!ctx || !A || !B_g2 || !H || !L || !g1c || !g2c || !out) return B200_ERR_ARG;
     if (A->group != 1 || B_g2->group != 2 || H->group != 1 || L->group != 1 || (B_g1 && (B_g1->group != 1 || B_g1->n != B_g2->n))) return B200_ERR_ARG;
-    if (L->n != num_variables - num_inputs) return B200_ERR_ARG;
+    if (L->n > num_variables - num_inputs) return B200_ERR_ARG;
     return Guard{ctx}.run([&] {
         std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
         k->ctx = ctx; k->owns_bases = false; k->full = B_g1 != nullptr;
@@ -267,6 +267,12 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
         *out = k.release();
         return (int)B200_OK;
     });
+}
+
+int b200_key_set_shard(b200_key* k, int rank, int world, uint64_t L_lo) {
+    if (!k || world < 1 || rank < 0 || rank >= world || k->has_circuit) return B200_ERR_ARG;
+    k->rank = rank; k->world = world; k->L_lo = L_lo;
+    return B200_OK;
 }
 
 void b200_key_free(b200_key* key) {
@@ -334,7 +340,7 @@ namespace {
 void run_witness_eval(b200_key* k, const uint64_t* witness) {
     b200_ctx* ctx = k->ctx;
     ctx->t_begin("h2d.witness");
-    B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyHostToDevice, ctx->stream));
+    B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
     ctx->t_end();
     ctx->t_begin("witness_eval");
     spmv(ctx, k->M[0], k->coeffs, k->d_w, k->d_a);

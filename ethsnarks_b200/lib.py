@@ -26,7 +26,7 @@ SYMBOLS = [
     "b200_g2_fixed_base", "b200_ntt", "b200_msm_g1", "b200_msm_g2", "b200_bases_upload", "b200_bases_generate",
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
-    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine",
+    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard",
 ]
 
 
@@ -114,6 +114,11 @@ class Context:
             self.lib.b200_timing_get(self.h, i, buf, C.c_size_t(64), C.byref(ms))
             out.append((buf.value.decode(), float(ms.value)))
         return out
+
+    def imad_peak(self, reps=5):
+        v = C.c_double()
+        self.check(self.lib.b200_imad_peak(self.h, reps, C.byref(v)), "imad_peak")
+        return float(v.value)
 
     # ---- sub-operations
     def field_op(self, field, op, a, b=None):
@@ -250,6 +255,9 @@ class ProvingKey:
             bi.ctypes.data_as(u32p) if bi is not None else None, H.h, L.h, _p64(g1c), _p64(g2c), C.c_uint64(num_variables),
             C.c_uint64(num_inputs), C.byref(h)), "key_from_bases")
         return ProvingKey(ctx, h, keep=(A, B_g2, B_g1, H, L))
+
+    def set_shard(self, rank, world, L_lo):
+        self.ctx.check(self.ctx.lib.b200_key_set_shard(self.h, rank, world, C.c_uint64(L_lo)), "key_set_shard")
 
     def info(self):
         out = np.zeros(8, np.uint64)

@@ -63,6 +63,10 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" 
 int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
 int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);
 
+/* integer-pipe probe: sustained 32x32+64-bit multiply-adds per second of this device (IMAD.WIDE.U32, all SMs) —
+ * the measured roofline denominator for the MSM / NTT kernels */
+int b200_imad_peak(b200_ctx* ctx, int reps, double* macs_per_s);
+
 /* ---- sub-operations (parity tests, config-5 MSM sweep) ---- */
 int b200_field_op(b200_ctx* ctx, int field /*0 Fr, 1 Fq*/, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
 int b200_g1_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf,
@@ -97,12 +101,16 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
                         const uint32_t* B_idx, b200_bases* H, b200_bases* L, const uint64_t* alpha_beta_delta_g1_xy /*3 x 8, mont*/,
                         const uint64_t* beta_delta_g2_xy /*2 x 16, mont*/, uint64_t num_variables, uint64_t num_inputs,
                         b200_key** out);
+/* multi-GPU with b200_key_from_bases: declare that A / B_g2 / L hold this rank's slice (L starting at entry L_lo of the
+ * full L query) and that H is the full query, to be sliced by rank at b200_circuit_load.  Call before circuit_load. */
+int b200_key_set_shard(b200_key* key, int rank, int world, uint64_t L_lo);
 void b200_key_free(b200_key* key);
 /* out[0..7]: domain_size (= num_variables + 1), |A|, |B|, |H|, |L| (this rank's counts), full(0/1), m, num_inputs */
 int b200_key_info(b200_key* key, uint64_t out[8]);
 int b200_circuit_load(b200_key* key, const b200_csr* A, const b200_csr* B, const b200_csr* C, const uint64_t* coeff_table_mont,
                       size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables);
-/* witness = full assignment, 4 * (num_variables + 1) limbs, w[0] = 1, Montgomery.  r = s = NULL: the reference's
+/* witness = full assignment, 4 * (num_variables + 1) limbs, w[0] = 1, Montgomery; a host pointer (pageable or pinned)
+ * or a device pointer (resident witness) — the copy is cudaMemcpyDefault.  r = s = NULL: the reference's
  * no-ZK prover.  Outputs: affine, STANDARD form (ready for proof_to_json), infinity flags for A, B, C. */
 int b200_prove(b200_key* key, const uint64_t* witness_mont, const uint64_t r_mont[4], const uint64_t s_mont[4],
                uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);

@@ -1,0 +1,278 @@
+"""GPU parity tests: every call goes through the C ABI (libb200snark.so) and is compared bit-for-bit with the CPU oracle
+on the same seeded inputs.  Run on the B200 box: python -m pytest tests -m gpu."""
+import json
+import numpy as np
+import pytest
+import orc
+import ethsnarks_b200 as eb
+from ethsnarks_b200 import lib as L
+
+pytestmark = pytest.mark.gpu
+
+
+def _edge_field_values(p):
+    vals = [0, 1, 2, p - 1, p - 2, (p - 1) // 2, 1 << 253, (1 << 253) - 1, p >> 1]
+    return orc.ints_to_arr([v % p for v in vals])
+
+
+@pytest.mark.parametrize("field,p", [(0, orc.R_MOD), (1, orc.Q_MOD)])
+def test_field_ops(ctx, field, p):
+    name = "fr" if field == 0 else "fq"
+    a = np.concatenate([orc.rand_fr_mont(5000, 11), _edge_field_values(p)])
+    b = np.concatenate([orc.rand_fr_mont(5000, 12), _edge_field_values(p)[::-1]])
+    for op, fn in ((L.OP_MUL, "_mul"), (L.OP_ADD, "_add"), (L.OP_SUB, "_sub")):
+        assert np.array_equal(ctx.field_op(field, op, a, b), getattr(orc, name + fn)(a, b)), fn
+    assert np.array_equal(ctx.field_op(field, L.OP_SQR, a), getattr(orc, name + "_mul")(a, a))
+    assert np.array_equal(ctx.field_op(field, L.OP_TO_MONT, a), getattr(orc, name + "_to_mont")(a))
+    assert np.array_equal(ctx.field_op(field, L.OP_FROM_MONT, a), getattr(orc, name + "_from_mont")(a))
+    assert np.array_equal(ctx.field_op(field, L.OP_INV, a[:300]), getattr(orc, name + "_inv")(a[:300]))
+    assert np.array_equal(ctx.field_op(field, L.OP_INV, a[-9:]), getattr(orc, name + "_inv")(a[-9:]))
+
+
+def test_fixed_base_and_group_law(ctx):
+    k = orc.sha512_rng_fr(1 << 40, 202)
+    k[0] = 0
+    k[1] = orc.constants()[8:12]   # scalar one
+    for group, gfix, ofix, gadd, oadd in ((1, ctx.g1_fixed_base, orc.g1_fixed_base, ctx.g1_add, orc.g1_add),
+                                          (2, ctx.g2_fixed_base, orc.g2_fixed_base, ctx.g2_add, orc.g2_add)):
+        xy, inf = gfix(k)
+        exy, einf = ofix(k)
+        assert np.array_equal(inf, einf) and inf[0] == 1
+        assert np.array_equal(xy[inf == 0], exy[einf == 0])
+        # group law incl. P+P, P+(-P), P+inf, inf+inf
+        w = 8 * group
+        a = xy[2:102].copy(); b = xy[102:202].copy()
+        ai = np.zeros(100, np.uint8); bi = np.zeros(100, np.uint8)
+        b[0] = a[0]                                   # doubling
+        neg = a[1].reshape(-1, 4).copy()              # P + (-P): negate y (last half of coordinates)
+        half = neg.shape[0] // 2
+        yneg = orc.fq_sub(np.zeros((half, 4), np.uint64), neg[half:])
+        b[1] = np.concatenate([neg[:half], yneg]).reshape(-1)
+        ai[2] = 1; bi[3] = 1; ai[4] = 1; bi[4] = 1
+        out, oinf = gadd(a, ai, b, bi)
+        for i in range(100):
+            e, ei = oadd(a[i], ai[i], b[i], bi[i])
+            assert oinf[i] == ei, i
+            if not ei:
+                assert np.array_equal(out[i], e), i
+        assert oinf[1] == 1 and oinf[4] == 1
+
+
+@pytest.mark.parametrize("logm", [1, 2, 5, 8, 10, 13, 16])
+def test_ntt_modes(ctx, logm):
+    x = orc.sha512_rng_fr(7 * logm, 1 << logm)
+    for mode in range(4):
+        assert np.array_equal(ctx.ntt(x, logm, mode), orc.ntt(x, logm, mode)), (logm, mode)
+    if logm <= 5:
+        assert np.array_equal(ctx.ntt(x, logm, 0), orc.dft_naive(x, logm))
+
+
+def test_ntt_large_roundtrip_and_linearity(ctx):
+    logm = 20
+    n = 1 << logm
+    x = orc.rand_fr_mont(n, 5); y = orc.rand_fr_mont(n, 6)
+    fx = ctx.ntt(x, logm, 0)
+    assert np.array_equal(ctx.ntt(fx, logm, 1), x)
+    assert np.array_equal(ctx.ntt(ctx.ntt(x, logm, 2), logm, 3), x)
+    assert np.array_equal(ctx.ntt(orc.fr_add(x, y), logm, 0), orc.fr_add(fx, ctx.ntt(y, logm, 0)))
+    assert np.array_equal(fx, orc.ntt(x, logm, 0))
+
+
+def _scalar_mix(n, seed, kind):
+    s = orc.sha512_rng_fr(seed, n)
+    one = orc.constants()[8:12]
+    if kind == "dense":
+        s[0] = 0; s[1 % n] = one
+        s[2 % n] = orc.fr_to_mont(orc.ints_to_arr([orc.R_MOD - 1]))[0]
+    elif kind == "binary":
+        rng = np.random.default_rng(seed)
+        sel = rng.integers(0, 10, n)
+        s[sel < 5] = 0
+        s[(sel >= 5) & (sel < 9)] = one
+    elif kind == "small":
+        s = orc.fr_to_mont(orc.ints_to_arr([int(v) for v in np.random.default_rng(seed).integers(0, 200, n)]))
+    return s
+
+
+@pytest.mark.parametrize("n,kind", [(1, "dense"), (2, "dense"), (33, "dense"), (1000, "dense"), (5000, "binary"),
+                                    (5000, "small"), (1 << 14, "dense"), (1 << 14, "binary")])
+def test_msm_g1_vs_oracle(ctx, n, kind):
+    k = orc.sha512_rng_fr((1 << 40) + n, n)
+    bases, inf = orc.g1_fixed_base(k)
+    if n > 10:
+        inf[5] = 1                     # a base at infinity
+        bases[7] = bases[6]            # repeated bases (doubling inside a bucket)
+        bases[9] = bases[8]
+    s = _scalar_mix(n, 1000 + n, kind)
+    if n > 10:
+        s[7] = s[6]; s[9] = orc.fr_sub(np.zeros((1, 4), np.uint64), s[8:9])[0]   # same bucket; opposite sign digits
+    got, ginf = ctx.msm_g1(bases, inf, s)
+    want, winf = orc.msm_g1(bases, inf, s)
+    assert ginf == winf
+    if not winf:
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("n,kind", [(1, "dense"), (37, "dense"), (3000, "dense"), (3000, "binary")])
+def test_msm_g2_vs_oracle(ctx, n, kind):
+    k = orc.sha512_rng_fr((1 << 41) + n, n)
+    bases, inf = orc.g2_fixed_base(k)
+    if n > 10:
+        inf[3] = 1; bases[7] = bases[6]
+    s = _scalar_mix(n, 2000 + n, kind)
+    got, ginf = ctx.msm_g2(bases, inf, s)
+    want, winf = orc.msm_g2(bases, inf, s)
+    assert ginf == winf and (winf or np.array_equal(got, want))
+
+
+def test_msm_edge_all_zero_and_cancel(ctx):
+    k = orc.sha512_rng_fr(99, 8)
+    bases, inf = orc.g1_fixed_base(k)
+    z = np.zeros((8, 4), np.uint64)
+    _, ginf = ctx.msm_g1(bases, inf, z)
+    assert ginf == 1
+    b2 = np.stack([bases[0], bases[0]]); s = orc.sha512_rng_fr(5, 1)
+    s2 = np.stack([s[0], orc.fr_sub(np.zeros((1, 4), np.uint64), s)[0]])
+    _, ginf = ctx.msm_g1(b2, None, s2)
+    assert ginf == 1
+
+
+@pytest.mark.parametrize("window", [0, 5, 11, 16])
+def test_msm_window_override(ctx, window):
+    n = 4000
+    bases, inf = orc.g1_fixed_base(orc.sha512_rng_fr(1 << 42, n))
+    s = _scalar_mix(n, 31, "dense")
+    ctx.set_option("window", window)
+    try:
+        got, ginf = ctx.msm_g1(bases, inf, s)
+    finally:
+        ctx.set_option("window", 0)
+    want, winf = orc.msm_g1(bases, inf, s)
+    assert ginf == winf and np.array_equal(got, want)
+
+
+def test_msm_large_in_the_exponent(ctx):
+    """2^20 distinct bases k_i*G generated on the GPU; MSM must equal (sum k_i s_i) * G."""
+    n = 1 << 20
+    k = orc.rand_fr_mont(n, 77); s = orc.rand_fr_mont(n, 78)
+    for group, fix in ((1, orc.g1_fixed_base), (2, orc.g2_fixed_base)):
+        bases = eb.Bases(ctx, group, scalars=k)
+        got, ginf = bases.msm(s)
+        want, winf = fix(orc.fr_dot(k, s).reshape(1, 4))
+        assert ginf == 0 and np.array_equal(got, want[0])
+        # 0/1-heavy mix (the giant "scalar == 1" bucket path)
+        sb = _scalar_mix(n, 5, "binary")
+        got, ginf = bases.msm(sb)
+        want, winf = fix(orc.fr_dot(k, sb).reshape(1, 4))
+        assert np.array_equal(got, want[0])
+        bases.free()
+
+
+def _load(ctx, circ, key, fmt_o, fmt_g, **kw):
+    pk = eb.ProvingKey.load(ctx, key.serialize(fmt_o), fmt_g, **kw)
+    pk.load_circuit(circ.matrix(0), circ.matrix(1), circ.matrix(2), circ.coeffs(), circ.ni, circ.nv)
+    return pk
+
+
+CIRCUITS = {
+    "field_30_3": lambda: orc.Circuit.synth_field(30, 3),
+    "field_1000_1": lambda: orc.Circuit.synth_field(1000, 1),
+    "binary_1000_10": lambda: orc.Circuit.synth_binary(1000, 10),
+    "field_5000_2": lambda: orc.Circuit.synth_field(5000, 2, 7, 8),
+}
+
+
+@pytest.mark.parametrize("name", list(CIRCUITS))
+def test_witness_eval_and_h(ctx, name):
+    circ = CIRCUITS[name]()
+    w = circ.witness()
+    key = orc.Key(circ)
+    pk = _load(ctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
+    h_want, ev = circ.h_poly(w, evals=True)
+    a, b, c = pk.witness_eval(w)
+    assert np.array_equal(a, ev[0][:circ.m]) and np.array_equal(b, ev[1][:circ.m]) and np.array_equal(c, ev[2][:circ.m])
+    h = pk.h_poly(w)
+    assert np.array_equal(h, h_want[:circ.m])
+    assert not h[circ.m - 1].any()
+    pk.free()
+
+
+@pytest.mark.parametrize("name", list(CIRCUITS))
+@pytest.mark.parametrize("fmt", ["mcl_nozk", "alt_full"])
+def test_prove_identical_to_oracle(ctx, name, fmt):
+    circ = CIRCUITS[name]()
+    w = circ.witness()
+    key = orc.Key(circ)
+    fo, fg = {"mcl_nozk": (orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK), "alt_full": (orc.FMT_ALT_FULL, eb.FMT_ALT_FULL)}[fmt]
+    pk = _load(ctx, circ, key, fo, fg)
+    got = pk.prove(w)
+    want = key.prove(w)
+    for g, e in zip(got, want):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    assert key.check_in_exponent(w, got) == 0
+    assert eb.proof_to_json(got, eb.host.fr_from_mont(w[1:1 + circ.ni])) == orc.proof_json(want, w[1:1 + circ.ni])
+    if fmt == "alt_full":   # r,s mode (libsnark r1cs_gg_ppzksnark formulas)
+        rs = orc.sha512_rng_fr(1 << 48, 2)
+        got = pk.prove(w, rs[0], rs[1])
+        want = key.prove(w, rs[0], rs[1])
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+        assert key.check_in_exponent(w, got, rs[0], rs[1]) == 0
+    pk.free()
+
+
+def test_proof_passes_pairing_verifier(ctx):
+    import pairing
+    circ = orc.Circuit.synth_field(30, 3)
+    w = circ.witness()
+    key = orc.Key(circ)
+    pk = _load(ctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
+    pj = json.loads(eb.proof_to_json(pk.prove(w), eb.host.fr_from_mont(w[1:1 + circ.ni])))
+    assert pairing.groth16_verify(json.loads(key.vk_json()), pj)
+    pk.free()
+
+
+def test_sharded_partials_combine_to_same_proof(ctx):
+    circ = orc.Circuit.synth_field(1000, 1)
+    w = circ.witness()
+    key = orc.Key(circ)
+    want = key.prove(w)
+    for world in (2, 3):
+        parts, flags = [], []
+        keys = [_load(ctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK, rank=r, world=world) for r in range(world)]
+        for k in keys:
+            p, f = k.prove_partial(w)
+            parts.append(p); flags.append(f)
+        got = keys[0].combine(np.stack(parts), np.stack(flags))
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+        for k in keys:
+            k.free()
+
+
+def test_host_mirror_prove_json(ctx):
+    pb = eb.generate_r1cs_example_with_field_input(200, 2)
+    circ = orc.Circuit.synth_field(200, 2)
+    assert eb.host.fr_from_mont(circ.witness()) == pb.values
+    key = orc.Key(circ)
+    pk = eb.load_proving_key(ctx, key.serialize(orc.FMT_MCL_NOZK))
+    pctx = eb.ProverContext(pk, pb)
+    assert pctx.domain == circ.m
+    js = eb.prove(pctx, pb)
+    assert js == orc.proof_json(key.prove(circ.witness()), circ.witness()[1:3])
+
+
+def test_error_paths(ctx):
+    with pytest.raises(eb.B200Error):
+        eb.ProvingKey.load(ctx, b"garbage", eb.FMT_MCL_NOZK)
+    circ = orc.Circuit.synth_field(30, 3)
+    key = orc.Key(circ)
+    pk = eb.ProvingKey.load(ctx, key.serialize(orc.FMT_MCL_NOZK), eb.FMT_MCL_NOZK)
+    with pytest.raises(eb.B200Error):
+        pk.prove(circ.witness())          # before circuit_load
+    pk.load_circuit(circ.matrix(0), circ.matrix(1), circ.matrix(2), circ.coeffs(), circ.ni, circ.nv)
+    rs = orc.sha512_rng_fr(1, 2)
+    with pytest.raises(eb.B200Error):
+        pk.prove(circ.witness(), rs[0], rs[1])   # r,s needs a FULL key
+    with pytest.raises(eb.B200Error):
+        eb.ProvingKey.load(ctx, key.serialize(orc.FMT_MCL_NOZK)[:-10], eb.FMT_MCL_NOZK)   # truncated
