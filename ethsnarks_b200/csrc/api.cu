@@ -141,6 +141,8 @@ struct b200_bases {
     int group = 1;
     size_t n = 0;
     void* d = nullptr;   // affine Montgomery, (0,0) = infinity
+    void* table = nullptr;   // optional window table [W][n] (b200_bases_precompute)
+    int table_c = 0;
 };
 
 extern "C" {
@@ -190,6 +192,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     if (!strcmp(name, "window")) ctx->window_override = (int)value;
     else if (!strcmp(name, "chunk")) ctx->chunk_override = (int)value;
     else if (!strcmp(name, "timing")) ctx->timing_enabled = value != 0;
+    else if (!strcmp(name, "precompute")) ctx->precompute = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;
 }
@@ -303,6 +306,21 @@ int b200_bases_generate(b200_ctx* ctx, int group, const uint64_t* scalars, size_
         return (int)B200_OK;
     });
 }
+int b200_bases_precompute(b200_bases* b, int window) {
+    if (!b || window < 0 || window > 24) return B200_ERR_ARG;
+    b200_ctx* ctx = b->ctx;
+    return Guard{ctx}.run([&] {
+        if (b->table) { cudaStreamSynchronize(ctx->stream); cudaFree(b->table); b->table = nullptr; b->table_c = 0; }
+        if (!b->n) return (int)B200_OK;
+        const int c = window ? std::max(4, window) : msm_table_window(b->n);
+        const int W = (255 + c - 1) / c;
+        B200_CUDA_CHECK(cudaMalloc(&b->table, (size_t)W * b->n * aff_bytes(b->group)));
+        g_precompute(ctx, b->group, b->d, b->n, c, b->table);
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        b->table_c = c;
+        return (int)B200_OK;
+    });
+}
 int b200_bases_download(b200_bases* b, uint64_t* xy, uint8_t* inf) {
     if (!b || !xy) return B200_ERR_ARG;
     return Guard{b->ctx}.run([&] { download_points(b->ctx, b->group, b->d, b->n, xy, inf); return (int)B200_OK; });
@@ -313,6 +331,7 @@ void b200_bases_free(b200_bases* b) {
     cudaSetDevice(b->ctx->device);
     cudaStreamSynchronize(b->ctx->stream);
     cudaFree(b->d);
+    cudaFree(b->table);
     delete b;
 }
 
@@ -329,7 +348,8 @@ int b200_msm(b200_ctx* ctx, b200_bases* bases, const uint64_t* scalars, size_t n
         }
         void* acc = ctx->scratch("msm_result", xyzz_bytes(g) + 256);
         void* fin = (char*)acc + xyzz_bytes(g);
-        msm_run(ctx, g, bases->d, d_scalars, nullptr, n, true, acc);
+        if (bases->table) msm_run(ctx, g, bases->table, d_scalars, nullptr, n, true, acc, bases->table_c, bases->n);
+        else msm_run(ctx, g, bases->d, d_scalars, nullptr, n, true, acc);
         g_finish(ctx, g, acc, 1, nullptr, 0, fin, false);
         ctx->t_end();
         fetch_finished(ctx, g, fin, out_xy, out_inf);

@@ -23,6 +23,7 @@ struct b200_ctx {
     unsigned long long launches = 0;   // kernels launched by this library since init
     int window_override = 0;           // 0 = cost model
     int chunk_override = 0;            // 0 = auto
+    int precompute = 1;                // build fixed-base window tables for resident keys / base sets
 
     void* scratch(const char* name, size_t bytes);   // throws std::runtime_error on failure
     void t_begin(const char* name);
@@ -46,7 +47,8 @@ namespace b200 {
 //   gathered: scalar_i = d_scalars[d_gather[i]].  d_bases: affine Montgomery, (0,0) = infinity.
 #define B200_DECL_GROUP(SUFFIX)                                                                                                   \
     void msm_run_##SUFFIX(b200_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_gather, size_t n,         \
-                          bool scalars_mont, void* d_out_xyzz);                                                                  \
+                          bool scalars_mont, void* d_out_xyzz, int table_c, size_t table_stride);                                \
+    void g_precompute_##SUFFIX(b200_ctx* ctx, const void* d_bases, size_t n, int c, void* d_table);                              \
     void g_finish_##SUFFIX(b200_ctx* ctx, const void* d_xyzz_terms, int n_terms, const void* d_affine_terms, int n_affine,       \
                            void* d_out_affine, bool to_std);                                                                     \
     void g_fixed_base_##SUFFIX(b200_ctx* ctx, const void* d_scalars_mont, size_t n, void* d_out_affine);                         \
@@ -56,9 +58,15 @@ B200_DECL_GROUP(g1)
 B200_DECL_GROUP(g2)
 // g_finish: out = sum(xyzz terms) + sum(affine terms) normalised to affine (Montgomery, or standard form if to_std),
 //           written as the affine point followed by a u32 infinity flag.
-inline void msm_run(b200_ctx* c, int group, const void* b, const void* s, const uint32_t* g, size_t n, bool mont, void* out) {
-    if (group == 1) msm_run_g1(c, b, s, g, n, mont, out); else msm_run_g2(c, b, s, g, n, mont, out);
+// table_c != 0: d_bases is a window table (table[w * table_stride + i] = 2^(table_c w) P_i) built by g_precompute
+inline void msm_run(b200_ctx* c, int group, const void* b, const void* s, const uint32_t* g, size_t n, bool mont, void* out,
+                    int table_c = 0, size_t table_stride = 0) {
+    if (group == 1) msm_run_g1(c, b, s, g, n, mont, out, table_c, table_stride); else msm_run_g2(c, b, s, g, n, mont, out, table_c, table_stride);
 }
+inline void g_precompute(b200_ctx* c, int group, const void* b, size_t n, int win, void* t) {
+    if (group == 1) g_precompute_g1(c, b, n, win, t); else g_precompute_g2(c, b, n, win, t);
+}
+int msm_table_window(size_t n);   // window size the cost model picks for a table over n bases
 inline void g_finish(b200_ctx* c, int group, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {
     if (group == 1) g_finish_g1(c, xt, nx, at, na, out, to_std); else g_finish_g2(c, xt, nx, at, na, out, to_std);
 }

@@ -2,4 +2,5 @@
 #include "msm_impl.cuh"
 namespace b200 {
 B200_INSTANTIATE_GROUP(G1T, g1)
+int msm_table_window(size_t n) { return choose_window(n, true); }
 }

@@ -52,7 +52,8 @@ template <> struct Gen<Fq2> {
 // ------------------------------------------------------------------------------------------------- 1. digits
 template <bool MONT>
 static __global__ void __launch_bounds__(256) msm_digits(const Fr* __restrict__ scalars, const uint32_t* __restrict__ gather, uint32_t n,
-                                                  int c, int W, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+                                                  int c, int W, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                  uint32_t stride, int table) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     Fr s = scalars[gather ? gather[i] : i];
@@ -61,7 +62,9 @@ static __global__ void __launch_bounds__(256) msm_digits(const Fr* __restrict__ 
 #pragma unroll
     for (int k = 0; k < 8; ++k) limb[k] = s.v[k];
     limb[8] = 0;
-    const uint32_t half = 1u << (c - 1), full = 1u << c, mask = full - 1, sentinel = (uint32_t)W * half;
+    // table mode: window w of point i uses the precomputed base 2^(c w) P_i at index w * stride + i, and every window
+    // feeds the same bucket set, so the key is the digit alone.
+    const uint32_t half = 1u << (c - 1), full = 1u << c, mask = full - 1, sentinel = table ? half : (uint32_t)W * half;
     uint32_t carry = 0;
     for (int w = 0; w < W; ++w) {
         uint32_t bit = (uint32_t)w * c, raw = 0;
@@ -72,8 +75,8 @@ static __global__ void __launch_bounds__(256) msm_digits(const Fr* __restrict__ 
         }
         uint32_t u = raw + carry, d, neg;
         if (u > half) { d = full - u; neg = 1; carry = 1; } else { d = u; neg = 0; carry = 0; }
-        keys[(size_t)w * n + i] = d ? (uint32_t)w * half + d - 1 : sentinel;
-        vals[(size_t)w * n + i] = i | (neg << 31);
+        keys[(size_t)w * n + i] = d ? (table ? 0u : (uint32_t)w * half) + d - 1 : sentinel;
+        vals[(size_t)w * n + i] = (table ? (uint32_t)w * stride + i : i) | (neg << 31);
     }
 }
 
@@ -231,28 +234,73 @@ __global__ void msm_horner(const typename G::Pt* __restrict__ win, int W, int c,
     *out = r;
 }
 
+// generic sum: out[b] = sum of in[b*R*128 .. (b+1)*R*128), one block of 128 threads per output point
+template <typename G>
+__global__ void __launch_bounds__(128) msm_tree_reduce(const typename G::Pt* __restrict__ in, uint32_t n, uint32_t R,
+                                                       typename G::Pt* __restrict__ out) {
+    typedef typename G::Pt Pt;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Pt* sh = reinterpret_cast<Pt*>(smem_raw);
+    const uint64_t base = (uint64_t)blockIdx.x * R * 128;
+    Pt acc = Pt::inf();
+    for (uint32_t r = 0; r < R; ++r) {
+        const uint64_t i = base + (uint64_t)r * 128 + threadIdx.x;
+        if (i < n) acc.add(in[i]);
+    }
+    block_tree_reduce(acc, sh);
+    if (threadIdx.x == 0) out[blockIdx.x] = acc;
+}
+
+// Fixed-base window tables for a resident key: table[w * n + i] = 2^(c w) * P_i, affine.  The proving key never
+// changes between proofs, so (like the reference generator's get_window_table, multiexp.tcc:771-807, but on the prover
+// side and held in HBM) every window of every base is materialised once at key load: all windows then share ONE
+// bucket set, the per-window bucket reductions and the 254-doubling window combine (multiexp.tcc:583-592) disappear.
+template <typename G>
+__global__ void __launch_bounds__(128) msm_precompute(const typename G::Aff* __restrict__ bases, size_t n, int c, int W,
+                                                      typename G::Aff* __restrict__ table) {
+    typedef typename G::Pt Pt;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const typename G::Aff b = bases[i];
+    table[i] = b;
+    Pt p = Pt::from_affine(b);
+    for (int w = 1; w < W; ++w) {
+        for (int k = 0; k < c; ++k) p.dbl();
+        table[(size_t)w * n + i] = p.to_affine();
+    }
+}
+
 // ------------------------------------------------------------------------------------------------- host side
 struct MsmPlan {
-    int c, W, keybits;
+    int c, W, keybits, table;
     uint32_t half, nb, L, S, nseg;
     uint64_t pairs, nchunks;
 };
 
-static MsmPlan make_plan(b200_ctx* ctx, size_t n, int group) {
-    MsmPlan p;
+// window size by cost model: N*W mixed adds (+ sort share) against the bucket reduction, which is paid once per window
+// without tables and once in total with them
+static int choose_window(size_t n, bool table) {
     int best_c = 8;
     double best = 1e300;
     const double add_cost = 10.0, full_cost = 14.0;
     for (int c = 6; c <= 22; ++c) {
         int W = (255 + c - 1) / c;
-        double cost = (double)n * W * (add_cost + 1.5 /* sort + digits share */) + (double)W * std::ldexp(1.0, c - 1) * (2 * full_cost + 6);
+        double cost = (double)n * W * (add_cost + 1.5 /* sort + digits share */) +
+                      (table ? 1.0 : (double)W) * std::ldexp(1.0, c - 1) * (2 * full_cost + 6);
         if (cost < best) { best = cost; best_c = c; }
     }
-    if (ctx->window_override) best_c = std::max(4, std::min(24, ctx->window_override));
+    return best_c;
+}
+
+static MsmPlan make_plan(b200_ctx* ctx, size_t n, int table_c) {
+    MsmPlan p;
+    int best_c = table_c ? table_c : choose_window(n, false);
+    if (ctx->window_override && !table_c) best_c = std::max(4, std::min(24, ctx->window_override));
+    p.table = table_c != 0;
     p.c = best_c;
     p.W = (255 + p.c - 1) / p.c;
     p.half = 1u << (p.c - 1);
-    p.nb = (uint32_t)p.W * p.half;
+    p.nb = p.table ? p.half : (uint32_t)p.W * p.half;
     p.keybits = 1;
     while ((1ull << p.keybits) <= p.nb) ++p.keybits;   // keys range over [0, nb] (nb = sentinel)
     p.pairs = (uint64_t)n * p.W;
@@ -266,13 +314,12 @@ static MsmPlan make_plan(b200_ctx* ctx, size_t n, int group) {
     S = std::min<uint32_t>(S, p.half);
     p.S = S;
     p.nseg = (p.half + S - 1) / S;
-    (void)group;
     return p;
 }
 
 template <typename G>
 static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_gather, size_t n, bool scalars_mont,
-                      void* d_out) {
+                      void* d_out, int table_c, size_t table_stride) {
     typedef typename G::Pt Pt;
     typedef typename G::Aff Aff;
     cudaStream_t st = ctx->stream;
@@ -284,7 +331,8 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
         return;
     }
     if (n >= (1ull << 31)) throw std::runtime_error("msm: n must be < 2^31");
-    MsmPlan p = make_plan(ctx, n, 0);
+    if (table_c && (uint64_t)table_stride * ((255 + table_c - 1) / table_c) >= (1ull << 31)) throw std::runtime_error("msm: table too large for 31-bit point indices");
+    MsmPlan p = make_plan(ctx, n, table_c);
     uint32_t* keys0 = (uint32_t*)ctx->scratch("msm_keys0", p.pairs * 4);
     uint32_t* keys1 = (uint32_t*)ctx->scratch("msm_keys1", p.pairs * 4);
     uint32_t* vals0 = (uint32_t*)ctx->scratch("msm_vals0", p.pairs * 4);
@@ -295,14 +343,14 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     Pt* plast = (Pt*)ctx->scratch("msm_plast", p.nchunks * sizeof(Pt));
     const size_t big_cap = p.nchunks / B200_BIG_SPAN + 2;
     uint32_t* big = (uint32_t*)ctx->scratch("msm_big", (big_cap + 1) * 4);
-    Pt* seg = (Pt*)ctx->scratch("msm_seg", (size_t)p.nseg * p.W * sizeof(Pt));
+    Pt* seg = (Pt*)ctx->scratch("msm_seg", ((size_t)p.nseg * p.W + p.nseg / 64 + 64) * sizeof(Pt));
     Pt* win = (Pt*)ctx->scratch("msm_win", (size_t)p.W * sizeof(Pt));
 
     ctx->t_begin("msm.digits");
     {
         dim3 grid((unsigned)((n + 255) / 256));
-        if (scalars_mont) msm_digits<true><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0);
-        else msm_digits<false><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0);
+        if (scalars_mont) msm_digits<true><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0, (uint32_t)table_stride, p.table);
+        else msm_digits<false><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0, (uint32_t)table_stride, p.table);
         ctx->launches++;
     }
     ctx->t_end();
@@ -335,16 +383,35 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     if (!attr_set[gi]) {
         B200_CUDA_CHECK(cudaFuncSetAttribute(msm_finalize_big<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         B200_CUDA_CHECK(cudaFuncSetAttribute(msm_window_reduce<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(msm_tree_reduce<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set[gi] = true;
     }
     msm_finalize_big<G><<<(unsigned)std::min<size_t>(big_cap, 1024), 128, smem, st>>>(offsets, p.L, buckets, pfirst, plast, big, big + 1);
     ctx->launches += 2;
     ctx->t_end();
     ctx->t_begin("msm.reduce");
-    msm_bucket_reduce<G><<<(p.nseg * p.W + 127) / 128, 128, 0, st>>>(buckets, p.half, p.S, p.nseg, p.W, seg);
-    msm_window_reduce<G><<<p.W, 128, smem, st>>>(seg, p.nseg, win);
-    msm_horner<G><<<1, 32, 0, st>>>(win, p.W, p.c, (Pt*)d_out);
-    ctx->launches += 3;
+    if (p.table) {
+        // one bucket set: segment sums, then a tree of block reductions straight into the result
+        msm_bucket_reduce<G><<<(p.nseg + 127) / 128, 128, 0, st>>>(buckets, p.half, p.S, p.nseg, 1, seg);
+        ctx->launches++;
+        Pt* cur = seg;
+        uint32_t cnt = p.nseg;
+        Pt* spare = seg + p.nseg;
+        while (true) {
+            const uint32_t R = cnt > 128 * 8 ? 8 : (cnt + 127) / 128;
+            const uint32_t blocks = (cnt + R * 128 - 1) / (R * 128);
+            Pt* dst = blocks == 1 ? (Pt*)d_out : spare;
+            msm_tree_reduce<G><<<blocks, 128, smem, st>>>(cur, cnt, R, dst);
+            ctx->launches++;
+            if (blocks == 1) break;
+            cur = dst; cnt = blocks; spare = dst + blocks;
+        }
+    } else {
+        msm_bucket_reduce<G><<<(p.nseg * p.W + 127) / 128, 128, 0, st>>>(buckets, p.half, p.S, p.nseg, p.W, seg);
+        msm_window_reduce<G><<<p.W, 128, smem, st>>>(seg, p.nseg, win);
+        msm_horner<G><<<1, 32, 0, st>>>(win, p.W, p.c, (Pt*)d_out);
+        ctx->launches += 3;
+    }
     ctx->t_end();
     B200_CUDA_CHECK(cudaGetLastError());
 }
@@ -443,11 +510,23 @@ static void g_scalar_mul_t(b200_ctx* ctx, const void* base, const void* scalar, 
 }
 
 
+// builds the window table for n resident bases; returns c via the plan the caller chose
+template <typename G>
+static void g_precompute_t(b200_ctx* ctx, const void* d_bases, size_t n, int c, void* d_table) {
+    if (n == 0) return;
+    const int W = (255 + c - 1) / c;
+    msm_precompute<G><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>((const typename G::Aff*)d_bases, n, c, W, (typename G::Aff*)d_table);
+    ctx->launches++;
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
 // Each group is instantiated in its own translation unit (msm_g1.cu / msm_g2.cu) so the two compile in parallel.
 #define B200_INSTANTIATE_GROUP(G, SUFFIX)                                                                                              \
-    void msm_run_##SUFFIX(b200_ctx* ctx, const void* b, const void* s, const uint32_t* g, size_t n, bool mont, void* out) {           \
-        msm_run_t<G>(ctx, b, s, g, n, mont, out);                                                                                      \
+    void msm_run_##SUFFIX(b200_ctx* ctx, const void* b, const void* s, const uint32_t* g, size_t n, bool mont, void* out, int tc,     \
+                          size_t ts) {                                                                                                 \
+        msm_run_t<G>(ctx, b, s, g, n, mont, out, tc, ts);                                                                              \
     }                                                                                                                                  \
+    void g_precompute_##SUFFIX(b200_ctx* ctx, const void* b, size_t n, int c, void* t) { g_precompute_t<G>(ctx, b, n, c, t); }         \
     void g_finish_##SUFFIX(b200_ctx* ctx, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {                   \
         g_finish_t<G>(ctx, xt, nx, at, na, out, to_std);                                                                               \
     }                                                                                                                                  \

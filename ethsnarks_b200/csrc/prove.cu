@@ -17,6 +17,8 @@ struct b200_bases {   // same definition as in api.cu
     int group;
     size_t n;
     void* d;
+    void* table;
+    int table_c;
 };
 
 struct b200_key {
@@ -30,6 +32,9 @@ struct b200_key {
     uint64_t H_lo = 0;          // first (bit-reversed) H position held by this rank
     void *A = nullptr, *B2 = nullptr, *B1 = nullptr, *H = nullptr, *L = nullptr;
     uint32_t *A_idx = nullptr, *B_idx = nullptr;
+    // fixed-base window tables (built at circuit_load when ctx->precompute): [W][n] affine, window size per query
+    void *A_t = nullptr, *B2_t = nullptr, *B1_t = nullptr, *H_t = nullptr, *L_t = nullptr;
+    int cA = 0, cB = 0, cH = 0, cL = 0;
     bool H_bitrev = false;      // H bases stored in bit-reversed order (needs the domain size: set at circuit_load)
     std::vector<uint8_t> H_host;   // natural-order H bases kept on the host until the domain size is known
     void* consts_g1 = nullptr;  // alpha_g1, beta_g1, delta_g1 (affine Montgomery)
@@ -122,6 +127,7 @@ void key_release(b200_key* k) {
     if (!k) return;
     if (k->owns_bases) { cudaFree(k->A); cudaFree(k->B2); cudaFree(k->B1); cudaFree(k->L); }
     cudaFree(k->H);
+    cudaFree(k->A_t); cudaFree(k->B2_t); cudaFree(k->B1_t); cudaFree(k->H_t); cudaFree(k->L_t);
     cudaFree(k->A_idx); cudaFree(k->B_idx); cudaFree(k->consts_g1); cudaFree(k->consts_g2);
     for (int i = 0; i < 3; ++i) csr_free(&k->M[i]);
     cudaFree(k->coeffs);
@@ -146,6 +152,29 @@ void place_h(b200_key* k) {
     k->H = dev_upload_bytes(buf.data(), buf.size());
     k->H_lo = lo; k->nH = hi - lo;
     k->H_bitrev = true;
+}
+
+void build_table(b200_key* k, int group, const void* pts, uint64_t n, void** table, int* c) {
+    cudaFree(*table);
+    *table = nullptr; *c = 0;
+    if (!k->ctx->precompute || !n || !pts) return;
+    const int win = k->ctx->window_override ? std::max(4, std::min(24, k->ctx->window_override)) : msm_table_window(n);
+    const int W = (255 + win - 1) / win;
+    const size_t bytes = (size_t)W * n * (group == 1 ? 64 : 128);
+    size_t free_b = 0, total_b = 0;
+    B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    if (bytes + (8ull << 30) > free_b) return;   // does not fit beside the MSM scratch: stay on the windowed path
+    B200_CUDA_CHECK(cudaMalloc(table, bytes));
+    g_precompute(k->ctx, group, pts, n, win, *table);
+    *c = win;
+}
+void build_tables(b200_key* k) {
+    build_table(k, 1, k->A, k->nA, &k->A_t, &k->cA);
+    build_table(k, 2, k->B2, k->nB, &k->B2_t, &k->cB);
+    if (k->full) { int cb1 = 0; build_table(k, 1, k->B1, k->nB, &k->B1_t, &cb1); if (cb1 != k->cB) { cudaFree(k->B1_t); k->B1_t = nullptr; } }
+    build_table(k, 1, k->H, k->nH, &k->H_t, &k->cH);
+    build_table(k, 1, k->L, k->nL, &k->L_t, &k->cL);
+    B200_CUDA_CHECK(cudaStreamSynchronize(k->ctx->stream));
 }
 
 }  // namespace
@@ -328,6 +357,7 @@ int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b
         B200_CUDA_CHECK(cudaMalloc(&k->d_b, k->m * 32));
         B200_CUDA_CHECK(cudaMalloc(&k->d_c, k->m * 32));
         place_h(k);
+        build_tables(k);
         return (int)B200_OK;
     });
 }
@@ -366,20 +396,20 @@ Acc acc_slots(b200_ctx* ctx) {
 void run_msms(b200_key* k, const Acc& a, bool want_b1) {
     b200_ctx* ctx = k->ctx;
     ctx->t_begin("msm.A");
-    msm_run(ctx, 1, k->A, k->d_w, k->A_idx, k->nA, true, a.A);
+    msm_run(ctx, 1, k->A_t ? k->A_t : k->A, k->d_w, k->A_idx, k->nA, true, a.A, k->A_t ? k->cA : 0, k->nA);
     ctx->t_end();
     ctx->t_begin("msm.B_g2");
-    msm_run(ctx, 2, k->B2, k->d_w, k->B_idx, k->nB, true, a.B2);
+    msm_run(ctx, 2, k->B2_t ? k->B2_t : k->B2, k->d_w, k->B_idx, k->nB, true, a.B2, k->B2_t ? k->cB : 0, k->nB);
     ctx->t_end();
     ctx->t_begin("msm.H");
-    msm_run(ctx, 1, k->H, (const char*)k->d_c + k->H_lo * 32, nullptr, k->nH, true, a.H);
+    msm_run(ctx, 1, k->H_t ? k->H_t : k->H, (const char*)k->d_c + k->H_lo * 32, nullptr, k->nH, true, a.H, k->H_t ? k->cH : 0, k->nH);
     ctx->t_end();
     ctx->t_begin("msm.L");
-    msm_run(ctx, 1, k->L, (const char*)k->d_w + (k->ni + 1 + k->L_lo) * 32, nullptr, k->nL, true, a.L);
+    msm_run(ctx, 1, k->L_t ? k->L_t : k->L, (const char*)k->d_w + (k->ni + 1 + k->L_lo) * 32, nullptr, k->nL, true, a.L, k->L_t ? k->cL : 0, k->nL);
     ctx->t_end();
     if (want_b1) {
         ctx->t_begin("msm.B_g1");
-        msm_run(ctx, 1, k->B1, k->d_w, k->B_idx, k->nB, true, a.B1);
+        msm_run(ctx, 1, k->B1_t ? k->B1_t : k->B1, k->d_w, k->B_idx, k->nB, true, a.B1, k->B1_t ? k->cB : 0, k->nB);
         ctx->t_end();
     }
 }

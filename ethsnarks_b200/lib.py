@@ -26,7 +26,7 @@ SYMBOLS = [
     "b200_g2_fixed_base", "b200_ntt", "b200_msm_g1", "b200_msm_g2", "b200_bases_upload", "b200_bases_generate",
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
-    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard",
+    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute",
 ]
 
 
@@ -196,6 +196,9 @@ class Bases:
             infp = _arr(inf, np.uint8).ctypes.data_as(u8p) if inf is not None else None
             ctx.check(ctx.lib.b200_bases_upload(ctx.h, group, _p64(xy), infp, C.c_size_t(n), C.byref(self.h)), "bases_upload")
         self.n = int(ctx.lib.b200_bases_count(self.h))
+
+    def precompute(self, window=0):
+        self.ctx.check(self.ctx.lib.b200_bases_precompute(self.h, window), "bases_precompute")
 
     def download(self):
         xy = np.zeros((self.n, 8 * self.group), np.uint64)

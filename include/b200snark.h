@@ -59,7 +59,7 @@ const char* b200_strerror(int code);
 const char* b200_last_error(b200_ctx* ctx);
 void* b200_stream(b200_ctx* ctx);                        /* the cudaStream_t every kernel of this ctx is launched on */
 unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by this library on ctx since b200_init */
-int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing" */
+int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing", "precompute" */
 int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
 int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);
 
@@ -84,6 +84,9 @@ int b200_msm_g2(b200_ctx* ctx, const uint64_t* bases_xy_mont, const uint8_t* inf
 /* ---- device-resident base sets (what a loaded key holds; used directly by the MSM sweep) ---- */
 int b200_bases_upload(b200_ctx* ctx, int group /*1|2*/, const uint64_t* xy_mont, const uint8_t* inf, size_t n, b200_bases** out);
 int b200_bases_generate(b200_ctx* ctx, int group, const uint64_t* scalars_mont, size_t n, b200_bases** out); /* k_i * generator */
+/* fixed-base window tables in HBM: table[w][i] = 2^(c w) * P_i for every window w, so later MSMs over this set use ONE
+ * bucket set and need no window combine.  window = 0: chosen by the cost model.  Costs ceil(255/c) x the base memory. */
+int b200_bases_precompute(b200_bases* bases, int window);
 int b200_bases_download(b200_bases* bases, uint64_t* xy_mont, uint8_t* inf);
 size_t b200_bases_count(b200_bases* bases);
 void b200_bases_free(b200_bases* bases);
