@@ -297,6 +297,8 @@ def run_ours(args):
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "phases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if not k.startswith("msm.") or k.split("#")[0] in
                       ("msm.A", "msm.B_g2", "msm.H", "msm.L")},
+        "msm_subphases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if k.startswith("msm.") and k.split("#")[0] not in
+                             ("msm.A", "msm.B_g2", "msm.H", "msm.L")},
         "msm_kernels": kernels,
     }
     if world == 1 and not args.no_cpu_baseline:

@@ -276,3 +276,36 @@ def test_error_paths(ctx):
         pk.prove(circ.witness(), rs[0], rs[1])   # r,s needs a FULL key
     with pytest.raises(eb.B200Error):
         eb.ProvingKey.load(ctx, key.serialize(orc.FMT_MCL_NOZK)[:-10], eb.FMT_MCL_NOZK)   # truncated
+
+
+def test_window_tables_on_and_off_give_the_same_results(ctx):
+    """Fixed-base window tables (b200_bases_precompute / key tables) vs the plain windowed path."""
+    n = 6000
+    k = orc.sha512_rng_fr((1 << 43), n)
+    s = _scalar_mix(n, 77, "dense")
+    for group, fix, omsm in ((1, orc.g1_fixed_base, orc.msm_g1), (2, orc.g2_fixed_base, orc.msm_g2)):
+        xy, inf = fix(k)
+        inf[11] = 1; xy[13] = xy[12]
+        want, winf = omsm(xy, inf, s)
+        b = eb.Bases(ctx, group, xy=xy, inf=inf)
+        got0, i0 = b.msm(s)
+        for window in (0, 7, 13):
+            b.precompute(window)
+            got1, i1 = b.msm(s)
+            assert i0 == i1 == winf and np.array_equal(got0, want) and np.array_equal(got1, want), (group, window)
+        got2, _ = b.msm(s[:1000], n=1000)          # a prefix of a tabled base set
+        want2, _ = omsm(xy[:1000], inf[:1000], s[:1000])
+        assert np.array_equal(got2, want2)
+        b.free()
+    circ = orc.Circuit.synth_binary(1000, 10); w = circ.witness(); key = orc.Key(circ)
+    want = key.prove(w)
+    for pre in (0, 1):
+        ctx.set_option("precompute", pre)
+        try:
+            pk = _load(ctx, circ, key, orc.FMT_MCL_FULL, eb.FMT_MCL_FULL)
+        finally:
+            ctx.set_option("precompute", 1)
+        got = pk.prove(w)
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e)), pre
+        pk.free()
