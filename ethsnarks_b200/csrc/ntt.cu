@@ -411,15 +411,14 @@ void witness_rows(b200_ctx* ctx, const void* d_w, void* d_a, void* d_b, void* d_
 // instruction the field multiplication is made of (the roofline denominator bench.py uses).
 __global__ void __launch_bounds__(256) imad_peak_kernel(uint64_t* out, uint32_t iters, uint32_t a0, uint32_t b0) {
     uint64_t acc[8];
-    uint32_t a = a0 + threadIdx.x, b = b0 + blockIdx.x;
+    const uint32_t a = a0 + threadIdx.x, b = b0 + blockIdx.x;
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = (uint64_t)(threadIdx.x + j) << 17;
     for (uint32_t i = 0; i < iters; ++i) {
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] = (uint64_t)a * (uint32_t)(b + j) + acc[j];
-            a = (uint32_t)acc[0] | 1u;
+            for (int j = 0; j < 8; ++j) acc[j] = (uint64_t)(a + r) * (uint32_t)(b + j) + acc[j];
         }
     }
     uint64_t s = 0;
@@ -427,26 +426,54 @@ __global__ void __launch_bounds__(256) imad_peak_kernel(uint64_t* out, uint32_t 
     for (int j = 0; j < 8; ++j) s ^= acc[j];
     if (s == 0x1234567ull) out[0] = s;   // practically never: keeps the chains live
 }
+// Same count of multiply-adds issued exactly as the field multiplication issues them: carry chains of four
+// mad.lo.cc / madc.hi.cc pairs (IMAD.WIDE.U32.X) on four independent 8-limb accumulators per thread.
+__global__ void __launch_bounds__(256) imad_chain_peak_kernel(uint64_t* out, uint32_t iters, uint32_t a0, uint32_t b0) {
+    uint32_t acc[4][8];
+    const uint32_t a = a0 + threadIdx.x, b = b0 + blockIdx.x;
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[s][j] = threadIdx.x * 977u + s * 31u + j;
+    for (uint32_t i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+#pragma unroll
+            for (int s = 0; s < 4; ++s) chain_mad(acc[s], a + s, a ^ 0x5bd1e995u, a + 0x9e3779b9u, a | 0x80000001u, b + r);
+        }
+    }
+    uint32_t x = 0;
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) x ^= acc[s][j];
+    if (x == 0x1234567u) out[0] = x;
+}
 double imad_peak(b200_ctx* ctx, int reps) {
     uint64_t* out = (uint64_t*)ctx->scratch("imad_peak", 64);
-    const uint32_t iters = 4096;
+    const uint32_t iters = 8192;
     const unsigned grid = (unsigned)ctx->sm_count * 8;
     cudaEvent_t e0, e1;
     B200_CUDA_CHECK(cudaEventCreate(&e0)); B200_CUDA_CHECK(cudaEventCreate(&e1));
-    imad_peak_kernel<<<grid, 256, 0, ctx->stream>>>(out, 64, 3, 5);   // warm-up
+    // warm-up long enough for the clocks to settle
+    for (int r = 0; r < 3; ++r) imad_peak_kernel<<<grid, 256, 0, ctx->stream>>>(out, iters, 3, 5);
     double best = 0;
     for (int r = 0; r < reps; ++r) {
-        B200_CUDA_CHECK(cudaEventRecord(e0, ctx->stream));
-        imad_peak_kernel<<<grid, 256, 0, ctx->stream>>>(out, iters, 3 + r, 5);
-        B200_CUDA_CHECK(cudaEventRecord(e1, ctx->stream));
-        B200_CUDA_CHECK(cudaEventSynchronize(e1));
-        float ms = 0;
-        B200_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
-        const double macs = (double)grid * 256 * iters * 32;
-        best = std::max(best, macs / (ms * 1e-3));
+        for (int variant = 0; variant < 2; ++variant) {
+            B200_CUDA_CHECK(cudaEventRecord(e0, ctx->stream));
+            if (variant == 0) imad_peak_kernel<<<grid, 256, 0, ctx->stream>>>(out, iters, 3 + r, 5);
+            else imad_chain_peak_kernel<<<grid, 256, 0, ctx->stream>>>(out, iters, 3 + r, 5);
+            B200_CUDA_CHECK(cudaEventRecord(e1, ctx->stream));
+            B200_CUDA_CHECK(cudaEventSynchronize(e1));
+            float ms = 0;
+            B200_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+            const double macs = (double)grid * 256 * iters * 32;   // both variants: 32 wide multiply-adds per iteration
+            best = std::max(best, macs / (ms * 1e-3));
+        }
     }
-    ctx->launches += reps + 1;
+    ctx->launches += 2 * reps + 3;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    B200_CUDA_CHECK(cudaGetLastError());
     return best;
 }
 
