@@ -11,9 +11,9 @@ using namespace b200;
 
 // ------------------------------------------------------------------------------------------------ ctx plumbing
 void* b200_ctx::scratch(const char* name, size_t bytes) {
-    Slot& s = slots[name];
+    Slot& s = slots[lane ? std::string(name) + "#" + std::to_string(lane) : std::string(name)];
     if (s.cap < bytes) {
-        if (s.p) { cudaStreamSynchronize(stream); cudaFree(s.p); s.p = nullptr; s.cap = 0; }
+        if (s.p) { cudaDeviceSynchronize(); cudaFree(s.p); s.p = nullptr; s.cap = 0; }
         size_t want = bytes + bytes / 8 + 256;
         cudaError_t e = cudaMalloc(&s.p, want);
         if (e != cudaSuccess) {
@@ -33,7 +33,7 @@ void b200_ctx::t_begin(const char* name) {
     if (!timing_enabled) return;
     cudaEvent_t a, b;
     cudaEventCreate(&a); cudaEventCreate(&b);
-    cudaEventRecord(a, stream);
+    cudaEventRecord(a, cur());
     timing_events.push_back({name, {a, b}});
 }
 void b200_ctx::t_end() {
@@ -41,7 +41,7 @@ void b200_ctx::t_end() {
     // close the most recent event pair that has not been closed yet (phases nest like a stack)
     for (size_t i = timing_events.size(); i-- > 0;) {
         if (timing_events[i].first.empty() || timing_events[i].first[0] != '#') {
-            cudaEventRecord(timing_events[i].second.second, stream);
+            cudaEventRecord(timing_events[i].second.second, cur());
             timing_events[i].first = "#" + timing_events[i].first;
             return;
         }
@@ -170,6 +170,10 @@ int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
     b200_ctx* c = new b200_ctx();
     c->device = dev;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return B200_ERR_CUDA; }
+    c->lanes[0] = c->stream;
+    for (int i = 1; i < 4; ++i) cudaStreamCreateWithFlags(&c->lanes[i], cudaStreamNonBlocking);
+    for (int i = 0; i < 4; ++i) cudaEventCreateWithFlags(&c->lane_done[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_witness, cudaEventDisableTiming);
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
     *out = c;
@@ -178,9 +182,12 @@ int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
 void b200_shutdown(b200_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    cudaDeviceSynchronize();
     for (auto& kv : ctx->slots) cudaFree(kv.second.p);
     ctx->t_collect();
+    for (int i = 1; i < 4; ++i) cudaStreamDestroy(ctx->lanes[i]);
+    for (int i = 0; i < 4; ++i) cudaEventDestroy(ctx->lane_done[i]);
+    cudaEventDestroy(ctx->ev_witness);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -193,6 +200,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "chunk")) ctx->chunk_override = (int)value;
     else if (!strcmp(name, "timing")) ctx->timing_enabled = value != 0;
     else if (!strcmp(name, "precompute")) ctx->precompute = (int)value;
+    else if (!strcmp(name, "overlap")) ctx->overlap = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;
 }

@@ -24,6 +24,14 @@ struct b200_ctx {
     int window_override = 0;           // 0 = cost model
     int chunk_override = 0;            // 0 = auto
     int precompute = 1;                // build fixed-base window tables for resident keys / base sets
+    // lanes: extra streams so the independent MSMs of one prove overlap (the latency-bound reduction tail of one MSM
+    // hides under the accumulate kernel of the next); each lane has its own scratch buffers
+    cudaStream_t lanes[4] = {nullptr, nullptr, nullptr, nullptr};   // lanes[0] == stream
+    cudaEvent_t lane_done[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_witness = nullptr;
+    int lane = 0;                      // lane the next kernels / scratch requests go to
+    int overlap = 1;
+    cudaStream_t cur() const { return lane ? lanes[lane] : stream; }
 
     void* scratch(const char* name, size_t bytes);   // throws std::runtime_error on failure
     void t_begin(const char* name);

@@ -322,7 +322,7 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
                       void* d_out, int table_c, size_t table_stride) {
     typedef typename G::Pt Pt;
     typedef typename G::Aff Aff;
-    cudaStream_t st = ctx->stream;
+    cudaStream_t st = ctx->cur();
     if (n == 0) {
         // empty sum = infinity
         Pt* out = (Pt*)d_out;

@@ -411,14 +411,16 @@ void witness_rows(b200_ctx* ctx, const void* d_w, void* d_a, void* d_b, void* d_
 // instruction the field multiplication is made of (the roofline denominator bench.py uses).
 __global__ void __launch_bounds__(256) imad_peak_kernel(uint64_t* out, uint32_t iters, uint32_t a0, uint32_t b0) {
     uint64_t acc[8];
-    const uint32_t a = a0 + threadIdx.x, b = b0 + blockIdx.x;
+    uint32_t a = a0 + threadIdx.x;
+    const uint32_t b = b0 + blockIdx.x;
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = (uint64_t)(threadIdx.x + j) << 17;
     for (uint32_t i = 0; i < iters; ++i) {
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
+            a ^= i + r;   // keeps the products loop-variant (ALU pipe, not counted)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] = (uint64_t)(a + r) * (uint32_t)(b + j) + acc[j];
+            for (int j = 0; j < 8; ++j) acc[j] = (uint64_t)a * (uint32_t)(b + j) + acc[j];
         }
     }
     uint64_t s = 0;

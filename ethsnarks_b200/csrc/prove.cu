@@ -371,6 +371,7 @@ void run_witness_eval(b200_key* k, const uint64_t* witness) {
     b200_ctx* ctx = k->ctx;
     ctx->t_begin("h2d.witness");
     B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
+    B200_CUDA_CHECK(cudaEventRecord(ctx->ev_witness, ctx->stream));
     ctx->t_end();
     ctx->t_begin("witness_eval");
     spmv(ctx, k->M[0], k->coeffs, k->d_w, k->d_a);
@@ -393,25 +394,41 @@ Acc acc_slots(b200_ctx* ctx) {
     a.A = base; a.H = base + 128; a.L = base + 256; a.B1 = base + 384; a.B2 = base + 512; a.tmp = base + 768; a.fin = base + 4096;
     return a;
 }
-void run_msms(b200_key* k, const Acc& a, bool want_b1) {
+// The A, B(G2), L (and B(G1)) MSMs need only the witness: they are queued on their own lanes right after the witness
+// upload and run concurrently with the witness map on the main stream; the H MSM follows the H chain on the main stream.
+void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1) {
     b200_ctx* ctx = k->ctx;
-    ctx->t_begin("msm.A");
-    msm_run(ctx, 1, k->A_t ? k->A_t : k->A, k->d_w, k->A_idx, k->nA, true, a.A, k->A_t ? k->cA : 0, k->nA);
-    ctx->t_end();
-    ctx->t_begin("msm.B_g2");
-    msm_run(ctx, 2, k->B2_t ? k->B2_t : k->B2, k->d_w, k->B_idx, k->nB, true, a.B2, k->B2_t ? k->cB : 0, k->nB);
-    ctx->t_end();
+    const bool ov = ctx->overlap != 0;
+    auto lane_begin = [&](int lane, const char* name) {
+        ctx->lane = ov ? lane : 0;
+        if (ctx->lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->lanes[lane], ctx->ev_witness, 0));
+        ctx->t_begin(name);
+    };
+    auto lane_end = [&]() {
+        ctx->t_end();
+        if (ctx->lane) B200_CUDA_CHECK(cudaEventRecord(ctx->lane_done[ctx->lane], ctx->lanes[ctx->lane]));
+        ctx->lane = 0;
+    };
+    try {
+        lane_begin(1, "msm.B_g2");
+        msm_run(ctx, 2, k->B2_t ? k->B2_t : k->B2, k->d_w, k->B_idx, k->nB, true, a.B2, k->B2_t ? k->cB : 0, k->nB);
+        lane_end();
+        lane_begin(2, "msm.A");
+        msm_run(ctx, 1, k->A_t ? k->A_t : k->A, k->d_w, k->A_idx, k->nA, true, a.A, k->A_t ? k->cA : 0, k->nA);
+        if (want_b1) msm_run(ctx, 1, k->B1_t ? k->B1_t : k->B1, k->d_w, k->B_idx, k->nB, true, a.B1, k->B1_t ? k->cB : 0, k->nB);
+        lane_end();
+        lane_begin(3, "msm.L");
+        msm_run(ctx, 1, k->L_t ? k->L_t : k->L, (const char*)k->d_w + (k->ni + 1 + k->L_lo) * 32, nullptr, k->nL, true, a.L, k->L_t ? k->cL : 0, k->nL);
+        lane_end();
+    } catch (...) { ctx->lane = 0; throw; }
+}
+void run_msm_h_and_join(b200_key* k, const Acc& a) {
+    b200_ctx* ctx = k->ctx;
     ctx->t_begin("msm.H");
     msm_run(ctx, 1, k->H_t ? k->H_t : k->H, (const char*)k->d_c + k->H_lo * 32, nullptr, k->nH, true, a.H, k->H_t ? k->cH : 0, k->nH);
     ctx->t_end();
-    ctx->t_begin("msm.L");
-    msm_run(ctx, 1, k->L_t ? k->L_t : k->L, (const char*)k->d_w + (k->ni + 1 + k->L_lo) * 32, nullptr, k->nL, true, a.L, k->L_t ? k->cL : 0, k->nL);
-    ctx->t_end();
-    if (want_b1) {
-        ctx->t_begin("msm.B_g1");
-        msm_run(ctx, 1, k->B1_t ? k->B1_t : k->B1, k->d_w, k->B_idx, k->nB, true, a.B1, k->B1_t ? k->cB : 0, k->nB);
-        ctx->t_end();
-    }
+    if (ctx->overlap)
+        for (int lane = 1; lane < 4; ++lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->lane_done[lane], 0));
 }
 void fetch(b200_ctx* ctx, int group, const void* d_fin, uint64_t* xy, uint8_t* inf) {
     uint8_t buf[128 + 16];
@@ -467,10 +484,11 @@ int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const 
     if (r && !k->full) { ctx->last_error = "r,s proving needs a FULL key (B query in G1)"; return B200_ERR_STATE; }
     return Guard{ctx}.run([&] {
         ctx->t_begin("prove.total");
-        run_witness_eval(k, witness);
-        run_h(k);
         Acc a = acc_slots(ctx);
-        run_msms(k, a, r != nullptr);
+        run_witness_eval(k, witness);
+        run_msms_witness_only(k, a, r != nullptr);
+        run_h(k);
+        run_msm_h_and_join(k, a);
         ctx->t_begin("finish");
         char* fin = (char*)a.fin;
         const char* c1 = (const char*)k->consts_g1;   // alpha, beta, delta (64 B each)
@@ -524,10 +542,11 @@ int b200_prove_partial(b200_key* k, const uint64_t* witness, uint64_t partial[32
     if (!k->has_circuit) { ctx->last_error = "prove_partial before circuit_load"; return B200_ERR_STATE; }
     return Guard{ctx}.run([&] {
         ctx->t_begin("prove.total");
-        run_witness_eval(k, witness);
-        run_h(k);
         Acc a = acc_slots(ctx);
-        run_msms(k, a, false);
+        run_witness_eval(k, witness);
+        run_msms_witness_only(k, a, false);
+        run_h(k);
+        run_msm_h_and_join(k, a);
         char* fin = (char*)a.fin;
         g_finish(ctx, 1, a.A, 1, nullptr, 0, fin, false);
         g_finish(ctx, 2, a.B2, 1, nullptr, 0, fin + 256, false);
