@@ -232,10 +232,16 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     phases = []
-    ms_dev, launches = timed(w_dev.data_ptr(), args.steps, phases)
+    ms_dev, launches = timed(w_dev.data_ptr(), args.steps, None)
     for _ in range(1):
         step(w_pin.data_ptr())
     ms_e2e, _ = timed(w_pin.data_ptr(), args.steps, None)
+    # per-kernel durations for the roofline: the same steps with the MSM lanes serialised, so that each kernel's
+    # CUDA-event bracket on its launching stream contains that kernel alone
+    ctx.set_option("overlap", 0)
+    step(w_dev.data_ptr())
+    timed(w_dev.data_ptr(), min(args.steps, 3), phases)
+    ctx.set_option("overlap", 1)
     clocks = sampler.stop() if rank == 0 else None
 
     proofs = args.steps * (1 if (shard or world == 1) else world)
