@@ -136,23 +136,45 @@ def build_workload(eb, ctx, log_m, rank, world):
 
 
 # ----------------------------------------------------------------------------------------------- CPU arm
-def cpu_prove_sample(sample_log_m, steps, warmup):
-    """Times the CPU implementation of the path (the oracle port of r1cs_gg_ppzksnark_zok_prover, OpenMP over all host
-    threads) on a 2^sample_log_m-constraint instance of the same synthetic R1CS; key generation excluded."""
+def cpu_prove_sample(sample_log_m, steps, warmup, target_log_m=None):
+    """Times the CPU implementation of the path on the host cores, key generation excluded.
+    If oracle/_ref/ref_prove exists (the reference's own prover templates built from /root/reference by
+    oracle/ref/Makefile) it is the thing timed (kind "reference", all OpenMP threads); otherwise the oracle port
+    (kind "port").  Returns (seconds per prove extrapolated to 2^target_log_m, threads, kind, description)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import orc
-    m = 1 << sample_log_m
-    circ = orc.Circuit.synth_field(m - 2, 1)
-    w = circ.witness()
-    key = orc.Key(circ)
-    times = []
-    for i in range(warmup + steps):
-        t0 = time.perf_counter()
-        key.prove(w)
-        dt = time.perf_counter() - t0
-        if i >= warmup:
-            times.append(dt)
-    return float(np.mean(times)), int(orc.lib().orc_num_threads())
+    import orc_ref
+    target_log_m = target_log_m or sample_log_m
+    use_ref = orc_ref.available()
+    threads = int(orc.lib().orc_num_threads())
+
+    def one(log_m):
+        m = 1 << log_m
+        circ = orc.Circuit.synth_field(m - 2, 1)
+        w = circ.witness()
+        key = orc.Key(circ)
+        if use_ref:
+            return orc_ref.prove(circ, w, key, repeats=warmup + steps)[2]   # best of the repeats, timed inside the binary
+        ts = []
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            key.prove(w)
+            if i >= warmup:
+                ts.append(time.perf_counter() - t0)
+        return float(np.mean(ts))
+
+    t_hi = one(sample_log_m)
+    if target_log_m == sample_log_m:
+        return t_hi, threads, "reference" if use_ref else "port", "2^%d-constraint instance, measured directly" % sample_log_m
+    # two-point fit T(m) = a + b m: the reference pays a fixed 2 * 2^16 bucket additions per window whatever the size
+    lo = max(10, sample_log_m - 2)
+    t_lo = one(lo)
+    b_ = (t_hi - t_lo) / ((1 << sample_log_m) - (1 << lo))
+    a_ = t_hi - b_ * (1 << sample_log_m)
+    sec = max(a_, 0.0) + b_ * (1 << target_log_m)
+    desc = ("proves of 2^%d- (%.2f s) and 2^%d-constraint (%.2f s) instances of the same R1CS on the host cores, "
+            "extrapolated T = a + b*m to 2^%d" % (lo, t_lo, sample_log_m, t_hi, target_log_m))
+    return sec, threads, "reference" if use_ref else "port", desc
 
 
 def run_reference(args):
@@ -160,17 +182,15 @@ def run_reference(args):
     if rank != 0:
         return
     sample_log = min(args.log_m, args.cpu_sample_log_m)
-    sec, cores = cpu_prove_sample(sample_log, args.steps, args.warmup)
-    scale = 1 << (args.log_m - sample_log)
-    value = 1.0 / (sec * scale)
-    sample = "2^%d-constraint instance of the same synthetic R1CS, %d timed proves; time scaled x%d to 2^%d" % (
-        sample_log, args.steps, scale, args.log_m)
+    sec, cores, kind, sample = cpu_prove_sample(sample_log, args.steps, args.warmup, args.log_m)
+    scale = 1
+    value = 1.0 / sec
     line = {
         "impl": "reference", "metric": "groth16_proofs_per_sec", "value": value, "unit": "proofs/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * scale * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery)", "data": "synthetic",
         "config": {"workload": "synthetic R1CS 2^%d constraints, full prove (4 MSMs + H NTT chain)" % args.log_m, "log_m": args.log_m},
-        "cpu_baseline": {"value": value, "unit": "proofs/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "proofs/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "proofs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -309,10 +329,8 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         sample_log = min(args.log_m, args.cpu_sample_log_m)
-        sec, cores = cpu_prove_sample(sample_log, 1, 0)
-        scale = 1 << (args.log_m - sample_log)
-        line["cpu_baseline"] = {"value": 1.0 / (sec * scale), "unit": "proofs/s", "cores": cores, "kind": "port",
-                                "sample": "one prove of a 2^%d-constraint instance of the same R1CS (%.2f s), scaled x%d" % (sample_log, sec, scale)}
+        sec, cores, kind, desc = cpu_prove_sample(sample_log, 1, 0, args.log_m)
+        line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "proofs/s", "cores": cores, "kind": kind, "sample": desc}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -326,7 +344,7 @@ def main():
     ap.add_argument("--log-m", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="shard", choices=["shard", "replicas"])
-    ap.add_argument("--cpu-sample-log-m", type=int, default=16)
+    ap.add_argument("--cpu-sample-log-m", type=int, default=17)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -1,0 +1,93 @@
+// oracle/_ref harness — TEST INFRASTRUCTURE ONLY.  Instantiates the REFERENCE's own prover templates
+// (libsnark::r1cs_gg_ppzksnark_zok_prover<libff::alt_bn128_pp>, src/r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.tcc:451-550)
+// from the sources under /root/reference, does the context set-up nobody in the reference does, and
+// runs one problem file written by tests/orc_ref.py:
+//   u64 nc, ni, nv, n_coeffs; coeffs (32 B mont each); for A, B, C: u64 nnz, row_ptr[nc+1] u64, col[nnz] u32, cidx[nnz] u32;
+//   witness (nv+1) x 32 B mont; u64 pk_len; pk bytes (ALT_NOZK layout = the reference's own operator<< under these flags)
+// Output file: A.x A.y | B.x.c0 B.x.c1 B.y.c0 B.y.c1 | C.x C.y as 32-byte standard-form little-endian integers, then
+// u64 m, then aH[0..m) (mont), then double seconds (the prover call, as "Call to r1cs_gg_ppzksnark_zok_prover").
+#include <fstream>
+#include <iostream>
+#include <sstream>
+#include <chrono>
+#include <omp.h>
+#include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
+#include <libfqfft/evaluation_domain/domains/basic_radix2_domain_aux.hpp>
+#include <libfqfft/evaluation_domain/domains/recursive_domain.hpp>
+#include "r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.hpp"
+
+typedef libff::alt_bn128_pp ppT;
+typedef libff::Fr<ppT> FieldT;
+using namespace libsnark;
+
+template <typename T> static void rd(std::istream& in, T& v) { in.read((char*)&v, sizeof(T)); }
+static FieldT rd_fr(std::istream& in) { FieldT f; in.read((char*)f.mont_repr.data, 32); return f; }
+template <typename F> static void wr_std(std::ostream& out, const F& f) { auto b = f.as_bigint(); out.write((const char*)b.data, 32); }
+
+int main(int argc, char** argv) {
+    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats]\n"; return 2; }
+    const int repeats = argc > 3 ? atoi(argv[3]) : 1;
+    ppT::init_public_params();
+    libff::inhibit_profiling_info = true;
+    libff::inhibit_profiling_counters = true;
+    std::ifstream in(argv[1], std::ios::binary);
+    if (!in) { std::cerr << "cannot open problem file\n"; return 2; }
+    uint64_t nc, ni, nv, ncoef;
+    rd(in, nc); rd(in, ni); rd(in, nv); rd(in, ncoef);
+    std::vector<unsigned int> cmap(ncoef);
+    for (uint64_t i = 0; i < ncoef; ++i) cmap[i] = ConstantStorage<FieldT>::getInstance().add(rd_fr(in));
+    r1cs_constraint_system<FieldT> cs;
+    cs.primary_input_size = ni;
+    cs.auxiliary_input_size = nv - ni;
+    std::vector<std::vector<linear_combination_light<FieldT>>> rows(3);
+    for (int k = 0; k < 3; ++k) {
+        uint64_t nnz; rd(in, nnz);
+        std::vector<uint64_t> rp(nc + 1); in.read((char*)rp.data(), 8 * (nc + 1));
+        std::vector<uint32_t> col(nnz), ci(nnz);
+        in.read((char*)col.data(), 4 * nnz); in.read((char*)ci.data(), 4 * nnz);
+        rows[k].resize(nc);
+        for (uint64_t r = 0; r < nc; ++r)
+            for (uint64_t j = rp[r]; j < rp[r + 1]; ++j) {
+                linear_term_light<FieldT> t; t.index = col[j]; t.coeff_index = cmap[ci[j]];
+                rows[k][r].terms.push_back(t);
+            }
+    }
+    for (uint64_t r = 0; r < nc; ++r)
+        cs.constraints.emplace_back(new r1cs_constraint_light<FieldT>(rows[0][r], rows[1][r], rows[2][r]));
+    std::vector<FieldT> w(nv + 1);
+    for (auto& x : w) x = rd_fr(in);
+    uint64_t pk_len; rd(in, pk_len);
+    std::string pk_bytes(pk_len, 0); in.read(&pk_bytes[0], pk_len);
+    r1cs_gg_ppzksnark_zok_proving_key_nozk<ppT> pk;
+    { std::istringstream ss(pk_bytes); ss >> pk; }
+
+    // the set-up the reference leaves to its (absent) caller: domain, constraint system pointer, m+1 buffers
+    libsnark::Config config;
+    uint64_t m = 1; while (m < nc + ni + 1) m <<= 1;
+    ProverContext<ppT> ctx(pk);
+    ctx.config = config;
+    ctx.constraint_system = &cs;
+    ctx.domain.reset(new libfqfft::recursive_domain<FieldT>(m, config));
+    ctx.aA.resize(m + 1); ctx.aB.resize(m + 1); ctx.aH.resize(m + 1);
+    ctx.scratch_exponents.resize(m + nv + 8);
+
+    double best = 1e30;
+    r1cs_gg_ppzksnark_zok_proof<ppT> proof;
+    for (int i = 0; i < repeats; ++i) {
+        auto t0 = std::chrono::steady_clock::now();
+        proof = r1cs_gg_ppzksnark_zok_prover<ppT>(ctx, w);
+        double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (dt < best) best = dt;
+    }
+    std::ofstream out(argv[2], std::ios::binary);
+    auto A = proof.g_A; A.to_affine_coordinates();
+    auto B = proof.g_B; B.to_affine_coordinates();
+    auto C = proof.g_C; C.to_affine_coordinates();
+    wr_std(out, A.X); wr_std(out, A.Y);
+    wr_std(out, B.X.c0); wr_std(out, B.X.c1); wr_std(out, B.Y.c0); wr_std(out, B.Y.c1);
+    wr_std(out, C.X); wr_std(out, C.Y);
+    out.write((const char*)&m, 8);
+    for (uint64_t i = 0; i < m; ++i) out.write((const char*)ctx.aH[i].mont_repr.data, 32);
+    out.write((const char*)&best, 8);
+    return 0;
+}

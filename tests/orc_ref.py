@@ -1,0 +1,48 @@
+"""Driver for oracle/_ref/ref_prove — the REFERENCE's own prover templates built from /root/reference by
+oracle/ref/Makefile.  TEST INFRASTRUCTURE ONLY.  Writes a problem file from oracle-side data, runs the reference binary,
+returns its proof points, its H coefficients and its prover time."""
+import os
+import struct
+import subprocess
+import tempfile
+import numpy as np
+import orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "ref_prove")
+
+
+def available():
+    return os.path.exists(REF_BIN)
+
+
+def write_problem(path, circ, w, pk_alt_nozk_bytes):
+    with open(path, "wb") as f:
+        coeffs = circ.coeffs()
+        f.write(struct.pack("<QQQQ", circ.nc, circ.ni, circ.nv, coeffs.shape[0]))
+        f.write(coeffs.tobytes())
+        for which in range(3):
+            rp, col, ci = circ.matrix(which)
+            f.write(struct.pack("<Q", len(col)))
+            f.write(np.ascontiguousarray(rp).tobytes()); f.write(np.ascontiguousarray(col).tobytes()); f.write(np.ascontiguousarray(ci).tobytes())
+        f.write(np.ascontiguousarray(w, dtype=np.uint64).tobytes())
+        f.write(struct.pack("<Q", len(pk_alt_nozk_bytes)))
+        f.write(pk_alt_nozk_bytes)
+
+
+def prove(circ, w, key, repeats=1, threads=None):
+    """returns ((A, B, C, inf) in the oracle's layout, H coefficients (m, 4) Montgomery, seconds)"""
+    with tempfile.TemporaryDirectory() as d:
+        prob, out = os.path.join(d, "problem.bin"), os.path.join(d, "out.bin")
+        write_problem(prob, circ, w, key.serialize(orc.FMT_ALT_NOZK))
+        env = dict(os.environ)
+        if threads:
+            env["OMP_NUM_THREADS"] = str(threads)
+        subprocess.run([REF_BIN, prob, out, str(repeats)], check=True, env=env, stdout=subprocess.DEVNULL)
+        raw = open(out, "rb").read()
+    pts = np.frombuffer(raw[:8 * 32], dtype=np.uint64).reshape(8, 4)
+    A = pts[0:2].reshape(-1).copy(); B = pts[2:6].reshape(-1).copy(); Cc = pts[6:8].reshape(-1).copy()
+    m = struct.unpack("<Q", raw[256:264])[0]
+    h = np.frombuffer(raw[264:264 + 32 * m], dtype=np.uint64).reshape(m, 4).copy()
+    sec = struct.unpack("<d", raw[264 + 32 * m:272 + 32 * m])[0]
+    return (A, B, Cc, np.zeros(3, np.uint8)), h, sec

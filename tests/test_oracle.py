@@ -120,3 +120,33 @@ def test_in_exponent_check_detects_tampering():
         bad = [np.array(x, copy=True) for x in pr]
         bad[idx][0] ^= np.uint64(1)
         assert k.check_in_exponent(w, tuple(bad)) != 0
+
+
+# ---- the reference's own prover templates, built by oracle/ref/Makefile into oracle/_ref (when present) ----
+import pytest  # noqa: E402
+import orc_ref  # noqa: E402
+
+needs_ref = pytest.mark.skipif(not orc_ref.available(), reason="oracle/_ref/ref_prove not built (needs /root/reference)")
+
+
+@needs_ref
+@pytest.mark.parametrize("mk", [lambda: orc.Circuit.synth_field(30, 3), lambda: orc.Circuit.synth_field(1000, 1),
+                                lambda: orc.Circuit.synth_binary(1000, 10), lambda: orc.Circuit.synth_field(5000, 2, 7, 8)])
+def test_oracle_equals_reference_build(mk):
+    """Proof points and all m coefficients of H from libsnark::r1cs_gg_ppzksnark_zok_prover<alt_bn128_pp> itself.
+    The reference is run single-threaded: with >= 2 OpenMP threads its own 0/1 prefilter races on a vector<bool>
+    (multiexp.tcc:652,692) and its proofs are not reproducible on small inputs."""
+    c = mk(); w = c.witness(); k = orc.Key(c)
+    (A, B, Cc, _), h, _ = orc_ref.prove(c, w, k, threads=1)
+    want = k.prove(w)
+    assert np.array_equal(A, want[0]) and np.array_equal(B, want[1]) and np.array_equal(Cc, want[2])
+    assert np.array_equal(h, c.h_poly(w)[:c.m])
+
+
+@needs_ref
+def test_reference_build_reads_the_oracle_key_bytes_and_matches_golden():
+    """The reference's operator>> accepts the oracle's ALT_NOZK serialisation, and the reference's proof for the golden
+    circuit renders to the committed golden JSON."""
+    c = orc.Circuit.synth_field(30, 3); w = c.witness(); k = orc.Key(c)
+    proof, _, _ = orc_ref.prove(c, w, k, threads=1)
+    assert orc.proof_json(proof, w[1:1 + c.ni]) == GOLD["circuits"]["field_30_3"]["proof_json"]
