@@ -1,16 +1,19 @@
 #!/usr/bin/env python
 """bench.py — Groth16 prove throughput on synthetic R1CS (BASELINE.json metric), one process per GPU.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--log-m 20] [--impl ours|reference] [--mode shard|replicas]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--log-m 20] [--impl ours|reference] [--mode both|shard|replicas]
 
 A "step" is one full prove (witness-times-R1CS, the 7-NTT H chain, the A / B(G2) / H / L multi-scalar
 multiplications, the final additions) of the synthetic 2^log_m-constraint R1CS of r1cs_examples.tcc:25-93 against a
 device-resident synthetic proving key of the matching shape.  `value` is measured with the witness already in HBM,
 `e2e` through the host-buffer C-ABI call (pinned witness H2D and proof D2H inside the timed region).
-With N > 1 (torchrun) every query of the key is split 1/N per rank, each rank proves its slice and only the three
-partial sums per rank (96 + 192 + 96 B... 35 x 8 B on the wire) are all-gathered over NCCL; rank 0 combines ("shard", strong
-scaling of one proof), or each rank proves independent witnesses ("replicas", weak scaling).
-`--impl reference` times the CPU implementation of the same path (the oracle port of the reference prover) instead.
+With N > 1 (torchrun) the headline `value` is N ranks proving independent witnesses against a resident key each
+("replicas", weak scaling: proofs are independent units, no data-path collective).  The same run also measures the
+north-star's MSM split and reports it under "sharded": every query of the key split 1/N per rank, each rank proves its
+slice, the three partial sums per rank (35 x 8 B) are all-gathered over NCCL and rank 0 combines (strong scaling of ONE
+proof's latency).  `--mode shard` / `--mode replicas` run one arrangement only.
+`--impl reference` times the CPU implementation of the same path (oracle/_ref, the reference's own prover built from its sources;
+else the oracle port) instead.
 """
 import argparse
 import json
@@ -214,12 +217,50 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     shard = world > 1 and args.mode == "shard"
     ctx = eb.Context(local)
+    imad_peak = ctx.imad_peak(5)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_steps(fn, steps, collect=None):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = ctx.launches
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+            if collect is not None:
+                collect.append(ctx.timings())
+        e1.record(stream)
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1), dev), ctx.launches - l0
+
+    # the other N>1 arrangement, measured in the same run and reported beside the headline: one proof with the key
+    # sharded 1/N per GPU (the north-star's MSM split; strong scaling, it shortens the latency of ONE proof)
+    sharded = None
+    if world > 1 and args.mode == "both":
+        skey, switness, _ = build_workload(eb, ctx, args.log_m, rank, world)
+        sw_dev = torch.from_numpy(switness.view(np.int64)).to(dev)
+
+        def sstep():
+            part, flags = skey.prove_partial(sw_dev.data_ptr())
+            parts, fl = gather_partials(part, flags, world, device=dev)
+            return skey.combine(parts, fl) if rank == 0 else None
+        for _ in range(max(args.warmup, 3)):
+            sstep()
+        sms, _ = timed_steps(sstep, args.steps)
+        sharded = {"scaling": "strong", "parallelism": "key sharded 1/%d per GPU, 35x8 B partial sums all-gathered over NCCL" % world,
+                   "latency_ms": sms / args.steps, "proofs_per_sec": args.steps / (sms * 1e-3)}
+        del skey, sw_dev
+        torch.cuda.synchronize()
+
     key, witness, dims = build_workload(eb, ctx, args.log_m, rank if shard else 0, world if shard else 1)
     nbytes_w = witness.nbytes
     w_dev = torch.from_numpy(witness.view(np.int64)).to(dev)            # resident witness (`value`)
     w_pin = torch.from_numpy(witness.view(np.int64)).pin_memory()       # pinned host witness (`e2e`)
-    stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
-    imad_peak = ctx.imad_peak(5)
 
     def step(wptr):
         if shard:
@@ -228,23 +269,8 @@ def run_ours(args):
             return key.combine(parts, fl) if rank == 0 else None
         return key.prove(wptr)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     def timed(wptr, steps, collect):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = ctx.launches
-        e0.record(stream)
-        for _ in range(steps):
-            step(wptr)
-            if collect is not None:
-                collect.append(ctx.timings())
-        e1.record(stream)
-        barrier()
-        return max_over_ranks(e0.elapsed_time(e1), dev), ctx.launches - l0
+        return timed_steps(lambda: step(wptr), steps, collect)
 
     for _ in range(max(args.warmup, 3)):
         step(w_dev.data_ptr())
@@ -270,17 +296,23 @@ def run_ours(args):
 
     # per-phase mean over the timed steps (names repeat: the k-th "msm.accumulate" belongs to the k-th MSM: A, B_g2, H, L)
     agg = {}
+    outer = ("msm.A", "msm.B_g2", "msm.B_g1", "msm.H", "msm.L")
     for tl in phases:
-        seen = {}
+        cur = None
         for name, ms in tl:
-            seen[name] = seen.get(name, 0) + 1
-            agg.setdefault("%s#%d" % (name, seen[name]), []).append(ms)
+            if name in outer:
+                cur = name[4:]
+                agg.setdefault(name, []).append(ms)
+            elif name.startswith("msm.") and cur:
+                agg.setdefault("%s@%s" % (name, cur), []).append(ms)
+            else:
+                agg.setdefault(name, []).append(ms)
     mean = {k: float(np.mean(v)) for k, v in agg.items()}
     msm_names = ["A", "B_g2", "H", "L"]
     counts = {"A": key.info()["nA"], "B_g2": key.info()["nB"], "H": key.info()["nH"], "L": key.info()["nL"]}
     kernels = {}
-    for i, nm in enumerate(msm_names):
-        ms = mean.get("msm.accumulate#%d" % (i + 1))
+    for nm in msm_names:
+        ms = mean.get("msm.accumulate@%s" % nm)
         if ms:
             g2 = nm == "B_g2"
             mac = (MAC_PER_G2_POINT if g2 else MAC_PER_G1_POINT) * counts[nm]
@@ -321,12 +353,12 @@ def run_ours(args):
         "e2e": {"value": e2e, "unit": "proofs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": int(nbytes_w),
                 "d2h_bytes_per_step": 64 + 128 + 64 + 3 * 4},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-        "phases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if not k.startswith("msm.") or k.split("#")[0] in
-                      ("msm.A", "msm.B_g2", "msm.H", "msm.L")},
-        "msm_subphases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if k.startswith("msm.") and k.split("#")[0] not in
-                             ("msm.A", "msm.B_g2", "msm.H", "msm.L")},
+        "phases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" not in k},
+        "msm_subphases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" in k},
         "msm_kernels": kernels,
     }
+    if sharded:
+        line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
         sample_log = min(args.log_m, args.cpu_sample_log_m)
         sec, cores, kind, desc = cpu_prove_sample(sample_log, 1, 0, args.log_m)
@@ -343,7 +375,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--log-m", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default="shard", choices=["shard", "replicas"])
+    ap.add_argument("--mode", default="both", choices=["both", "shard", "replicas"])
     ap.add_argument("--cpu-sample-log-m", type=int, default=17)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -49,12 +49,15 @@ void b200_ctx::t_end() {
 }
 void b200_ctx::t_collect() {
     timings.clear();
+    timing_starts.clear();
     for (auto& ev : timing_events) {
-        float ms = 0.f;
+        float ms = 0.f, at = 0.f;
         if (!ev.first.empty() && ev.first[0] == '#') cudaEventElapsedTime(&ms, ev.second.first, ev.second.second);
+        cudaEventElapsedTime(&at, timing_events.front().second.first, ev.second.first);
+        timing_starts.push_back(at);
         timings.push_back({ev.first.empty() ? ev.first : ev.first.substr(ev.first[0] == '#' ? 1 : 0), ms});
-        cudaEventDestroy(ev.second.first); cudaEventDestroy(ev.second.second);
     }
+    for (auto& ev : timing_events) { cudaEventDestroy(ev.second.first); cudaEventDestroy(ev.second.second); }
     timing_events.clear();
 }
 
@@ -169,9 +172,17 @@ int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
     if (cudaSetDevice(dev) != cudaSuccess) return B200_ERR_CUDA;
     b200_ctx* c = new b200_ctx();
     c->device = dev;
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return B200_ERR_CUDA; }
+    // Stream priorities order the tails: lane 1 (the G2 MSM, the longest chain) first, then the main stream (H chain and
+    // H MSM), then the two witness-only G1 lanes, whose accumulate blocks fill the SMs the latency-bound reductions of
+    // the higher-priority chains leave idle.
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);   // numerically lower = higher priority
+    auto prio = [&](int level) { return std::max(prio_hi, std::min(prio_lo, prio_lo - level)); };
+    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio(1)) != cudaSuccess) { delete c; return B200_ERR_CUDA; }
     c->lanes[0] = c->stream;
-    for (int i = 1; i < 4; ++i) cudaStreamCreateWithFlags(&c->lanes[i], cudaStreamNonBlocking);
+    cudaStreamCreateWithPriority(&c->lanes[1], cudaStreamNonBlocking, prio(2));
+    cudaStreamCreateWithPriority(&c->lanes[2], cudaStreamNonBlocking, prio(0));
+    cudaStreamCreateWithPriority(&c->lanes[3], cudaStreamNonBlocking, prio(0));
     for (int i = 0; i < 4; ++i) cudaEventCreateWithFlags(&c->lane_done[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_witness, cudaEventDisableTiming);
     cudaDeviceProp prop;
@@ -201,6 +212,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "timing")) ctx->timing_enabled = value != 0;
     else if (!strcmp(name, "precompute")) ctx->precompute = (int)value;
     else if (!strcmp(name, "overlap")) ctx->overlap = (int)value;
+    else if (!strcmp(name, "reduce_1d")) ctx->reduce_1d = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;
 }
@@ -209,6 +221,12 @@ int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms) {
     if (!ctx || i < 0 || i >= (int)ctx->timings.size()) return B200_ERR_ARG;
     if (name && cap) { strncpy(name, ctx->timings[i].first.c_str(), cap - 1); name[cap - 1] = 0; }
     if (ms) *ms = ctx->timings[i].second;
+    return B200_OK;
+}
+
+int b200_timing_start(b200_ctx* ctx, int i, float* ms) {
+    if (!ctx || !ms || i < 0 || i >= (int)ctx->timing_starts.size()) return B200_ERR_ARG;
+    *ms = ctx->timing_starts[i];
     return B200_OK;
 }
 

@@ -11,6 +11,15 @@
 namespace b200 {
 
 // Affine point; the pair (0, 0) is not on either curve (b != 0) and encodes the point at infinity.
+// Out-of-line group operations: one copy per translation unit instead of one per call site.  Only the mixed addition of
+// the accumulate kernel is worth inlining; every other use (reductions, helpers) is latency-bound and the inlined
+// bodies (a G2 addition is ~10^4 instructions) only cost compile time and instruction cache.
+#ifdef B200_COLD_INLINE
+#define B200_DEV_COLD __device__ __forceinline__
+#else
+#define B200_DEV_COLD __device__ __noinline__
+#endif
+
 template <typename F>
 struct Affine {
     F x, y;
@@ -30,7 +39,7 @@ struct XYZZ {
     }
 
     // 2 * (affine p), p not at infinity   (mdbl-2008-s-1)
-    static B200_DEV XYZZ dbl_affine(const Affine<F>& p) {
+    static B200_DEV_COLD XYZZ dbl_affine(const Affine<F>& p) {
         F U = p.y.dbl();
         if (U.is_zero()) return inf();
         F V = U.sqr(), W = U * V, S = p.x * V;
@@ -43,7 +52,7 @@ struct XYZZ {
         return r;
     }
     // this = 2 * this   (dbl-2008-s-1)
-    B200_DEV void dbl() {
+    B200_DEV_COLD void dbl() {
         if (is_inf()) return;
         F U = Y.dbl();
         if (U.is_zero()) { *this = inf(); return; }
@@ -72,7 +81,7 @@ struct XYZZ {
         ZZ = ZZ * PP; ZZZ = ZZZ * PPP;
     }
     // this += o   (add-2008-s: 12M + 2S), complete
-    B200_DEV void add(const XYZZ& o) {
+    B200_DEV_COLD void add(const XYZZ& o) {
         if (o.is_inf()) return;
         if (is_inf()) { *this = o; return; }
         F U1 = X * o.ZZ, U2 = o.X * ZZ, S1 = Y * o.ZZZ, S2 = o.Y * ZZZ;

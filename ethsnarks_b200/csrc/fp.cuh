@@ -262,14 +262,25 @@ struct Fq2 {
     friend B200_DEV Fq2 operator-(const Fq2& x, const Fq2& y) { return Fq2{x.a - y.a, x.b - y.b}; }
     B200_DEV Fq2 neg() const { return Fq2{a.neg(), b.neg()}; }
     B200_DEV Fq2 dbl() const { return Fq2{a.dbl(), b.dbl()}; }
+#ifndef B200_FQ2_OOL
+#define B200_FQ2_OOL 0      // 1: the Fq products inside Fq2 are calls to one out-of-line copy (smaller code)
+#endif
+    static __device__ __noinline__ Fq mul_ool(Fq x, Fq y) { return x * y; }
+    static B200_DEV Fq fqmul(const Fq& x, const Fq& y) {
+#if B200_FQ2_OOL
+        return mul_ool(x, y);
+#else
+        return x * y;
+#endif
+    }
     friend B200_DEV Fq2 operator*(const Fq2& x, const Fq2& y) {   // Karatsuba, 3 Fq products
-        Fq aa = x.a * y.a, bb = x.b * y.b;
-        Fq m = (x.a + x.b) * (y.a + y.b);
+        Fq aa = fqmul(x.a, y.a), bb = fqmul(x.b, y.b);
+        Fq m = fqmul(x.a + x.b, y.a + y.b);
         return Fq2{aa - bb, m - aa - bb};
     }
     B200_DEV Fq2 sqr() const {   // complex squaring, 2 Fq products
-        Fq ab = a * b;
-        return Fq2{(a + b) * (a - b), ab.dbl()};
+        Fq ab = fqmul(a, b);
+        return Fq2{fqmul(a + b, a - b), ab.dbl()};
     }
     B200_DEV Fq2 inv() const {
         Fq n = (a.sqr() + b.sqr()).inv();

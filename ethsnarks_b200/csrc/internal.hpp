@@ -19,10 +19,12 @@ struct b200_ctx {
     // phase timings of the last prove / msm / h call (CUDA events on `stream`)
     std::vector<std::pair<std::string, std::pair<cudaEvent_t, cudaEvent_t>>> timing_events;
     std::vector<std::pair<std::string, float>> timings;
+    std::vector<float> timing_starts;   // start of each phase relative to the first phase of the call, ms
     bool timing_enabled = true;
     unsigned long long launches = 0;   // kernels launched by this library since init
     int window_override = 0;           // 0 = cost model
     int chunk_override = 0;            // 0 = auto
+    int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one
     int precompute = 1;                // build fixed-base window tables for resident keys / base sets
     // lanes: extra streams so the independent MSMs of one prove overlap (the latency-bound reduction tail of one MSM
     // hides under the accumulate kernel of the next); each lane has its own scratch buffers

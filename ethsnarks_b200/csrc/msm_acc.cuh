@@ -1,0 +1,49 @@
+#pragma once
+// The hot kernel of the MSM (stage 4 of msm_common.cuh's list) and its launcher.
+#include "msm_common.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------- 4. accumulate
+template <typename G>
+__global__ void __launch_bounds__(128, G::kAccMinBlocks) msm_accumulate(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                                      const uint64_t* __restrict__ offsets, uint32_t nb, uint32_t L,
+                                                      const typename G::Aff* __restrict__ bases, typename G::Pt* __restrict__ buckets,
+                                                      typename G::Pt* __restrict__ pfirst, typename G::Pt* __restrict__ plast) {
+    typedef typename G::Pt Pt;
+    typedef typename G::Aff Aff;
+    const uint64_t M = offsets[nb];
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t start = t * L;
+    if (start >= M) return;
+    const uint64_t end = min(start + (uint64_t)L, M);
+    uint32_t cur = keys[start];
+    bool first_run = true;
+    Pt acc = Pt::inf();
+    for (uint64_t i = start; i < end; ++i) {
+        const uint32_t k = keys[i];
+        if (k != cur) {
+            if (first_run) pfirst[t] = acc; else buckets[cur] = acc;
+            first_run = false;
+            acc = Pt::inf();
+            cur = k;
+        }
+        const uint32_t v = vals[i];
+        Aff p = bases[v & 0x7fffffffu];
+        if (v >> 31) p.y = p.y.neg();
+        acc.add_mixed(p);
+    }
+    if (first_run) pfirst[t] = acc; else plast[t] = acc;
+}
+
+
+template <typename G>
+void launch_accumulate(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* skeys, const uint32_t* svals,
+                       const uint64_t* offsets, const void* d_bases, void* buckets, void* pfirst, void* plast) {
+    typedef typename G::Pt Pt;
+    msm_accumulate<G><<<(unsigned)((p.nchunks + 127) / 128), 128, 0, st>>>(skeys, svals, offsets, p.nb, p.L, (const typename G::Aff*)d_bases,
+                                                                            (Pt*)buckets, (Pt*)pfirst, (Pt*)plast);
+    ctx->launches++;
+}
+
+}  // namespace b200

@@ -1,5 +1,5 @@
-// G2 instantiation of the MSM pipeline and group helpers (see msm_impl.cuh).
+// G2 MSM orchestration (msm_impl.cuh): digits, sort, offsets and the stage launchers.
 #include "msm_impl.cuh"
 namespace b200 {
-B200_INSTANTIATE_GROUP(G2T, g2)
+B200_INSTANTIATE_GROUP_RUN(G2T, g2)
 }

@@ -1,0 +1,294 @@
+#pragma once
+// Stages 5 and 6 of the MSM (msm_common.cuh): stitching chunk partial sums into buckets, and the bucket reductions.
+#include "msm_common.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------- 5. finalize
+template <typename G>
+__global__ void __launch_bounds__(128) msm_finalize(const uint64_t* __restrict__ offsets, uint32_t nb, uint32_t L,
+                                                    typename G::Pt* __restrict__ buckets, const typename G::Pt* __restrict__ pfirst,
+                                                    const typename G::Pt* __restrict__ plast, uint32_t* __restrict__ big_count,
+                                                    uint32_t* __restrict__ big_list) {
+    typedef typename G::Pt Pt;
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb) return;
+    const uint64_t M = offsets[nb];
+    const uint64_t s = offsets[b], e = offsets[b + 1];
+    if (s == e) { buckets[b] = Pt::inf(); return; }
+    const uint64_t t0 = s / L, t1 = (e - 1) / L;
+    if (t0 == t1) {
+        const bool first = (s == t0 * L);
+        const bool last = (e == min((t0 + 1) * (uint64_t)L, M));
+        if (first) buckets[b] = pfirst[t0];
+        else if (last) buckets[b] = plast[t0];
+        return;   // otherwise msm_accumulate already wrote the complete run
+    }
+    if (t1 - t0 > B200_BIG_SPAN) { big_list[atomicAdd(big_count, 1u)] = b; return; }
+    Pt acc = (s == t0 * L) ? pfirst[t0] : plast[t0];
+    for (uint64_t t = t0 + 1; t <= t1; ++t) acc.add(pfirst[t]);
+    buckets[b] = acc;
+}
+
+template <typename Pt>
+B200_DEV void block_tree_reduce(Pt& acc, Pt* sh) {   // blockDim.x == 128; result in thread 0's acc
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int stride = 64; stride > 0; stride >>= 1) {
+        if ((int)threadIdx.x < stride) {
+            Pt a = sh[threadIdx.x];
+            a.add(sh[threadIdx.x + stride]);
+            sh[threadIdx.x] = a;
+        }
+        __syncthreads();
+    }
+    acc = sh[0];
+    __syncthreads();
+}
+
+template <typename G>
+__global__ void __launch_bounds__(128) msm_finalize_big(const uint64_t* __restrict__ offsets, uint32_t L,
+                                                        typename G::Pt* __restrict__ buckets, const typename G::Pt* __restrict__ pfirst,
+                                                        const typename G::Pt* __restrict__ plast, const uint32_t* __restrict__ big_count,
+                                                        const uint32_t* __restrict__ big_list) {
+    typedef typename G::Pt Pt;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Pt* sh = reinterpret_cast<Pt*>(smem_raw);
+    const uint32_t nbig = *big_count;
+    for (uint32_t j = blockIdx.x; j < nbig; j += gridDim.x) {
+        const uint32_t b = big_list[j];
+        const uint64_t s = offsets[b], e = offsets[b + 1];
+        const uint64_t t0 = s / L, t1 = (e - 1) / L;
+        Pt acc = Pt::inf();
+        if (threadIdx.x == 0) acc = (s == t0 * L) ? pfirst[t0] : plast[t0];
+        for (uint64_t t = t0 + 1 + threadIdx.x; t <= t1; t += blockDim.x) acc.add(pfirst[t]);
+        block_tree_reduce(acc, sh);
+        if (threadIdx.x == 0) buckets[b] = acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------- 6. reductions
+// one thread per segment of S consecutive buckets of one window: sum_{b in seg} (b+1) * B_b
+template <typename G>
+__global__ void __launch_bounds__(128) msm_bucket_reduce(const typename G::Pt* __restrict__ buckets, uint32_t half, uint32_t S,
+                                                         uint32_t nseg, int W, typename G::Pt* __restrict__ seg) {
+    typedef typename G::Pt Pt;
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= nseg * (uint32_t)W) return;
+    const uint32_t w = id / nseg, sidx = id % nseg;
+    const uint32_t lo = sidx * S, hi = min(lo + S, half);
+    const Pt* B = buckets + (size_t)w * half;
+    Pt acc = Pt::inf(), sum = Pt::inf();
+    for (uint32_t lb = hi; lb-- > lo;) {
+        acc.add(B[lb]);
+        sum.add(acc);
+    }
+    if (lo && !acc.is_inf()) sum.add(acc.mul_u32(lo));
+    seg[id] = sum;
+}
+// one block per output: out[w] = sum of seg[w*nseg .. min((w+1)*nseg, total))
+template <typename G>
+__global__ void __launch_bounds__(128) msm_window_reduce(const typename G::Pt* __restrict__ seg, uint32_t nseg, uint32_t total,
+                                                         typename G::Pt* __restrict__ win) {
+    typedef typename G::Pt Pt;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Pt* sh = reinterpret_cast<Pt*>(smem_raw);
+    const uint32_t w = blockIdx.x;
+    const uint32_t lo = w * nseg, hi = min(lo + nseg, total);
+    Pt acc = Pt::inf();
+    for (uint32_t s = lo + threadIdx.x; s < hi; s += blockDim.x) acc.add(seg[s]);
+    block_tree_reduce(acc, sh);
+    if (threadIdx.x == 0) win[w] = acc;
+}
+// ---- two-dimensional bucket reduction --------------------------------------------------------------------------
+// The running-sum reduction above is a chain of 2*S dependent additions per thread; at 2^19 buckets that chain, not the
+// arithmetic, sets the time.  Here the buckets of a window are a matrix [Rn rows][S = 2^s columns], b = hi*S + lo, and
+//     sum_b (b+1) B_b  =  sum_lo (lo+1) C_lo  +  S * sum_hi hi R_hi ,   C = column sums, R = row sums,
+// so the bulk of the work (2 additions per bucket) is plain sums with no dependence between threads (stages A, B).
+// The two short weighted sums are taken bit by bit: U_i = sum of the C_lo with bit i of (lo+1) set plus the R_hi with
+// bit (i-s) of hi set, then sum_i 2^i U_i with the 2^i applied by i doublings in parallel (stages C, D, E).
+// Stage A: K-term partial column sums pc[g][lo] and partial row sums pr[hi][lg].
+template <typename G>
+__global__ void __launch_bounds__(128) msm_rc_partial(const typename G::Pt* __restrict__ buckets, uint32_t half, uint32_t s, uint32_t K,
+                                                      typename G::Pt* __restrict__ pc, typename G::Pt* __restrict__ pr) {
+    typedef typename G::Pt Pt;
+    const uint32_t S = 1u << s, Rn = half >> s;
+    const uint32_t Kc = min(K, Rn), Kr = min(K, S);
+    const uint32_t ncol = (Rn / Kc) * S, nrow = Rn * (S / Kr);
+    const Pt* B = buckets + (size_t)blockIdx.y * half;
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id < ncol) {
+        const uint32_t g = id >> s, lo = id & (S - 1);
+        const Pt* src = B + (size_t)g * Kc * S + lo;
+        Pt acc = src[0];
+        for (uint32_t k = 1; k < Kc; ++k) acc.add(src[(size_t)k * S]);
+        pc[(size_t)blockIdx.y * ncol + id] = acc;
+        return;
+    }
+    id -= ncol;
+    if (id >= nrow) return;
+    const Pt* src = B + (size_t)id * Kr;     // row hi = id / (S/Kr), group lg = id % (S/Kr): consecutive buckets
+    Pt acc = src[0];
+    for (uint32_t k = 1; k < Kr; ++k) acc.add(src[k]);
+    pr[(size_t)blockIdx.y * nrow + id] = acc;
+}
+// Warp-level tree sum of one point per lane; the result is in lane 0.  The stages below run one warp per output so that
+// no resident warp sits idle at a block barrier holding 255 registers per thread.
+template <typename Pt>
+B200_DEV void warp_tree_reduce(Pt& acc) {
+    constexpr int NW = sizeof(Pt) / 4;
+    const uint32_t lane = threadIdx.x & 31;
+#pragma unroll 1
+    for (int off = 16; off > 0; off >>= 1) {
+        Pt other;
+        uint32_t* o = reinterpret_cast<uint32_t*>(&other);
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(&acc);
+#pragma unroll
+        for (int w = 0; w < NW; ++w) o[w] = __shfl_down_sync(0xffffffffu, a[w], off);
+        if (lane < (uint32_t)off) acc.add(other);
+    }
+}
+// Stage B: one warp per column (blockIdx.x < S) or row: V[lo] = C_lo, V[S + hi] = R_hi.
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_sum(const typename G::Pt* __restrict__ pc, const typename G::Pt* __restrict__ pr,
+                                                 uint32_t half, uint32_t s, uint32_t K, typename G::Pt* __restrict__ V) {
+    typedef typename G::Pt Pt;
+    const uint32_t S = 1u << s, Rn = half >> s;
+    const uint32_t Kc = min(K, Rn), Kr = min(K, S);
+    const uint32_t ncol = (Rn / Kc) * S, nrow = Rn * (S / Kr);
+    const uint32_t o = blockIdx.x;
+    const Pt* src;
+    uint32_t cnt, stride;
+    if (o < S) { src = pc + (size_t)blockIdx.y * ncol + o; cnt = Rn / Kc; stride = S; }
+    else { src = pr + (size_t)blockIdx.y * nrow + (size_t)(o - S) * (S / Kr); cnt = S / Kr; stride = 1; }
+    Pt acc = Pt::inf();
+    for (uint32_t t = threadIdx.x; t < cnt; t += 32) acc.add(src[(size_t)t * stride]);
+    warp_tree_reduce(acc);
+    if (threadIdx.x == 0) V[(size_t)blockIdx.y * (S + Rn) + o] = acc;
+}
+// Stage C: one warp per (weight bit i, slice of B200_RC_SLICE entries of V): sum of the selected C_lo and R_hi.
+#define B200_RC_SLICE 128
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_bits(const typename G::Pt* __restrict__ V, uint32_t half, uint32_t s,
+                                                  uint32_t nbits, uint32_t nslice, typename G::Pt* __restrict__ Us) {
+    typedef typename G::Pt Pt;
+    const uint32_t S = 1u << s, Rn = half >> s;
+    const uint32_t i = blockIdx.x / nslice, sl = blockIdx.x % nslice;
+    const Pt* v = V + (size_t)blockIdx.z * (S + Rn);
+    Pt acc = Pt::inf();
+    const uint32_t end = min((sl + 1) * B200_RC_SLICE, S + Rn);
+    for (uint32_t t = sl * B200_RC_SLICE + threadIdx.x; t < end; t += 32) {
+        const uint32_t weight = t < S ? t + 1 : (t - S) << s;
+        if ((weight >> i) & 1u) acc.add(v[t]);
+    }
+    warp_tree_reduce(acc);
+    if (threadIdx.x == 0) Us[((size_t)blockIdx.z * nbits + i) * nslice + sl] = acc;
+}
+// Stage D: one warp per weight bit: U_i = 2^i * (sum of its slices).
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_shift(const typename G::Pt* __restrict__ Us, uint32_t nbits, uint32_t nslice,
+                                                   typename G::Pt* __restrict__ U) {
+    typedef typename G::Pt Pt;
+    const uint32_t i = blockIdx.x;
+    const Pt* src = Us + ((size_t)blockIdx.z * nbits + i) * nslice;
+    Pt acc = Pt::inf();
+    for (uint32_t t = threadIdx.x; t < nslice; t += 32) acc.add(src[t]);
+    warp_tree_reduce(acc);
+    if (threadIdx.x == 0) {
+        for (uint32_t k = 0; k < i; ++k) acc.dbl();
+        U[(size_t)blockIdx.z * nbits + i] = acc;
+    }
+}
+// Stage E: one warp per window: sum of its U_i (nbits <= 32).
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_final(const typename G::Pt* __restrict__ U, uint32_t nbits, typename G::Pt* __restrict__ out) {
+    typedef typename G::Pt Pt;
+    Pt acc = Pt::inf();
+    if (threadIdx.x < nbits) acc = U[(size_t)blockIdx.x * nbits + threadIdx.x];
+    warp_tree_reduce(acc);
+    if (threadIdx.x == 0) out[blockIdx.x] = acc;
+}
+
+// final = sum_k 2^(c k) win[k]   (the reference's combine, multiexp.tcc:583-592)
+template <typename G>
+__global__ void msm_horner(const typename G::Pt* __restrict__ win, int W, int c, typename G::Pt* __restrict__ out) {
+    typedef typename G::Pt Pt;
+    if (threadIdx.x || blockIdx.x) return;
+    Pt r = Pt::inf();
+    for (int w = W - 1; w >= 0; --w) {
+        for (int i = 0; i < c; ++i) r.dbl();
+        r.add(win[w]);
+    }
+    *out = r;
+}
+
+// ------------------------------------------------------------------------------------------------- launchers
+template <typename G>
+void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint64_t* offsets, void* buckets_, const void* pfirst_,
+                     const void* plast_, uint32_t* big, size_t big_cap) {
+    typedef typename G::Pt Pt;
+    Pt* buckets = (Pt*)buckets_;
+    const Pt* pfirst = (const Pt*)pfirst_;
+    const Pt* plast = (const Pt*)plast_;
+    const size_t smem = 128 * sizeof(Pt);     // <= 32 KB, inside the default dynamic shared memory limit
+    B200_CUDA_CHECK(cudaMemsetAsync(big, 0, 4, st));
+    msm_finalize<G><<<(p.nb + 127) / 128, 128, 0, st>>>(offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+    msm_finalize_big<G><<<(unsigned)std::min<size_t>(big_cap, 1024), 128, smem, st>>>(offsets, p.L, buckets, pfirst, plast, big, big + 1);
+    ctx->launches += 2;
+}
+
+template <typename G>
+void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void* buckets_, void* seg_, void* win_, void* d_out) {
+    typedef typename G::Pt Pt;
+    const Pt* B = (const Pt*)buckets_;
+    Pt* seg = (Pt*)seg_;
+    Pt* win = (Pt*)win_;
+    const size_t smem = 128 * sizeof(Pt);
+    const int Wr = p.table ? 1 : p.W;                 // bucket sets to reduce
+    if (p.half >= 1024 && !ctx->reduce_1d) {
+        // two-dimensional reduction (see msm_rc_partial): four launches, no long dependent chain
+        const uint32_t s = (uint32_t)(p.c - 1 + 1) / 2, S = 1u << s, Rn = p.half >> s, K = 8;
+        const uint32_t Kc = std::min(K, Rn), Kr = std::min(K, S);
+        const uint32_t ncol = (Rn / Kc) * S, nrow = Rn * (S / Kr);
+        const uint32_t nbits = std::max<uint32_t>(s + 1, (uint32_t)p.c - 1);
+        Pt* pc = (Pt*)ctx->scratch("msm_rc_pc", (size_t)Wr * ncol * sizeof(Pt));
+        Pt* pr = (Pt*)ctx->scratch("msm_rc_pr", (size_t)Wr * nrow * sizeof(Pt));
+        Pt* V = (Pt*)ctx->scratch("msm_rc_v", (size_t)Wr * (S + Rn) * sizeof(Pt));
+        Pt* U = (Pt*)ctx->scratch("msm_rc_u", (size_t)Wr * nbits * sizeof(Pt));
+        const uint32_t nslice = (S + Rn + B200_RC_SLICE - 1) / B200_RC_SLICE;
+        Pt* Us = (Pt*)ctx->scratch("msm_rc_us", (size_t)Wr * nbits * nslice * sizeof(Pt));
+        msm_rc_partial<G><<<dim3((ncol + nrow + 127) / 128, Wr), 128, 0, st>>>(B, p.half, s, K, pc, pr);
+        msm_rc_sum<G><<<dim3(S + Rn, Wr), 32, 0, st>>>(pc, pr, p.half, s, K, V);
+        msm_rc_bits<G><<<dim3(nbits * nslice, 1, Wr), 32, 0, st>>>(V, p.half, s, nbits, nslice, Us);
+        msm_rc_shift<G><<<dim3(nbits, 1, Wr), 32, 0, st>>>(Us, nbits, nslice, U);
+        msm_rc_final<G><<<Wr, 32, 0, st>>>(U, nbits, p.table ? (Pt*)d_out : win);
+        ctx->launches += 5;
+        if (!p.table) {
+            msm_horner<G><<<1, 32, 0, st>>>(win, p.W, p.c, (Pt*)d_out);
+            ctx->launches++;
+        }
+    } else if (p.table) {
+        // one bucket set: segment sums, then a tree of block reductions straight into the result
+        msm_bucket_reduce<G><<<(p.nseg + 127) / 128, 128, 0, st>>>(B, p.half, p.S, p.nseg, 1, seg);
+        ctx->launches++;
+        Pt* cur = seg;
+        uint32_t cnt = p.nseg;
+        Pt* spare = seg + p.nseg;
+        while (true) {
+            const uint32_t per = cnt > 128 * 8 ? 128 * 8 : cnt;        // inputs per block
+            const uint32_t blocks = (cnt + per - 1) / per;
+            Pt* dst = blocks == 1 ? (Pt*)d_out : spare;
+            msm_window_reduce<G><<<blocks, 128, smem, st>>>(cur, per, cnt, dst);
+            ctx->launches++;
+            if (blocks == 1) break;
+            cur = dst; cnt = blocks; spare = dst + blocks;
+        }
+    } else {
+        msm_bucket_reduce<G><<<(p.nseg * p.W + 127) / 128, 128, 0, st>>>(B, p.half, p.S, p.nseg, p.W, seg);
+        msm_window_reduce<G><<<p.W, 128, smem, st>>>(seg, p.nseg, p.nseg * (uint32_t)p.W, win);
+        msm_horner<G><<<1, 32, 0, st>>>(win, p.W, p.c, (Pt*)d_out);
+        ctx->launches += 3;
+    }
+}
+
+}  // namespace b200

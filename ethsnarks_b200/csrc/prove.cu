@@ -396,8 +396,11 @@ Acc acc_slots(b200_ctx* ctx) {
 }
 // The A, B(G2), L (and B(G1)) MSMs need only the witness: they are queued on their own lanes right after the witness
 // upload and run concurrently with the witness map on the main stream; the H MSM follows the H chain on the main stream.
-void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1) {
+// finish: 0 = leave the sums in XYZZ; 1 = the no-ZK prover's g_A = alpha + sum A and g_B = beta + sum B (standard form)
+// right on the lane that produced the sum, so only g_C is left for the join; 2 = plain affine partial sums (sharded key).
+void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1, int finish = 0) {
     b200_ctx* ctx = k->ctx;
+    char* fin = (char*)a.fin;
     const bool ov = ctx->overlap != 0;
     auto lane_begin = [&](int lane, const char* name) {
         ctx->lane = ov ? lane : 0;
@@ -412,10 +415,14 @@ void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1) {
     try {
         lane_begin(1, "msm.B_g2");
         msm_run(ctx, 2, k->B2_t ? k->B2_t : k->B2, k->d_w, k->B_idx, k->nB, true, a.B2, k->B2_t ? k->cB : 0, k->nB);
+        if (finish == 1) g_finish(ctx, 2, a.B2, 1, k->consts_g2, 1, fin + 256, true);
+        if (finish == 2) g_finish(ctx, 2, a.B2, 1, nullptr, 0, fin + 256, false);
         lane_end();
         lane_begin(2, "msm.A");
         msm_run(ctx, 1, k->A_t ? k->A_t : k->A, k->d_w, k->A_idx, k->nA, true, a.A, k->A_t ? k->cA : 0, k->nA);
         if (want_b1) msm_run(ctx, 1, k->B1_t ? k->B1_t : k->B1, k->d_w, k->B_idx, k->nB, true, a.B1, k->B1_t ? k->cB : 0, k->nB);
+        if (finish == 1) g_finish(ctx, 1, a.A, 1, k->consts_g1, 1, fin, true);
+        if (finish == 2) g_finish(ctx, 1, a.A, 1, nullptr, 0, fin, false);
         lane_end();
         lane_begin(3, "msm.L");
         msm_run(ctx, 1, k->L_t ? k->L_t : k->L, (const char*)k->d_w + (k->ni + 1 + k->L_lo) * 32, nullptr, k->nL, true, a.L, k->L_t ? k->cL : 0, k->nL);
@@ -486,7 +493,7 @@ int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const 
         ctx->t_begin("prove.total");
         Acc a = acc_slots(ctx);
         run_witness_eval(k, witness);
-        run_msms_witness_only(k, a, r != nullptr);
+        run_msms_witness_only(k, a, r != nullptr, r ? 0 : 1);
         run_h(k);
         run_msm_h_and_join(k, a);
         ctx->t_begin("finish");
@@ -494,8 +501,7 @@ int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const 
         const char* c1 = (const char*)k->consts_g1;   // alpha, beta, delta (64 B each)
         const char* c2 = (const char*)k->consts_g2;   // beta, delta (128 B each)
         if (!r) {
-            g_finish(ctx, 1, a.A, 1, c1, 1, fin, true);                  // g_A = alpha_g1 + evaluation_At
-            g_finish(ctx, 2, a.B2, 1, c2, 1, fin + 256, true);           // g_B = beta_g2 + evaluation_Bt
+            // g_A = alpha_g1 + evaluation_At and g_B = beta_g2 + evaluation_Bt were finished on their lanes
             g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, true);       // g_C = evaluation_Ht + evaluation_Lt (H, L adjacent)
         } else {
             // scalars r, s, -(r s) on the device
@@ -544,12 +550,10 @@ int b200_prove_partial(b200_key* k, const uint64_t* witness, uint64_t partial[32
         ctx->t_begin("prove.total");
         Acc a = acc_slots(ctx);
         run_witness_eval(k, witness);
-        run_msms_witness_only(k, a, false);
+        run_msms_witness_only(k, a, false, 2);
         run_h(k);
         run_msm_h_and_join(k, a);
         char* fin = (char*)a.fin;
-        g_finish(ctx, 1, a.A, 1, nullptr, 0, fin, false);
-        g_finish(ctx, 2, a.B2, 1, nullptr, 0, fin + 256, false);
         g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, false);
         ctx->t_end();
         fetch(ctx, 1, fin, partial, &flags[0]);

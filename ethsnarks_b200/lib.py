@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libb200snark.so")
+SO_PATH = os.environ.get("B200SNARK_LIB") or os.path.join(_HERE, "libb200snark.so")   # the override is for kernel experiments
 
 u64p = C.POINTER(C.c_uint64)
 u32p = C.POINTER(C.c_uint32)
@@ -22,7 +22,7 @@ NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT = range(4)
 # every symbol include/b200snark.h declares (tests check the .so exports all of them)
 SYMBOLS = [
     "b200_init", "b200_shutdown", "b200_strerror", "b200_last_error", "b200_stream", "b200_launch_count", "b200_set_option",
-    "b200_timing_count", "b200_timing_get", "b200_field_op", "b200_g1_add", "b200_g2_add", "b200_g1_fixed_base",
+    "b200_timing_count", "b200_timing_get", "b200_timing_start", "b200_field_op", "b200_g1_add", "b200_g2_add", "b200_g1_fixed_base",
     "b200_g2_fixed_base", "b200_ntt", "b200_msm_g1", "b200_msm_g2", "b200_bases_upload", "b200_bases_generate",
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
@@ -113,6 +113,15 @@ class Context:
         for i in range(n):
             self.lib.b200_timing_get(self.h, i, buf, C.c_size_t(64), C.byref(ms))
             out.append((buf.value.decode(), float(ms.value)))
+        return out
+
+    def timeline(self):
+        """(name, start_ms, duration_ms) of every phase of the last call; start is relative to its first phase."""
+        at = C.c_float()
+        out = []
+        for i, (name, ms) in enumerate(self.timings()):
+            self.lib.b200_timing_start(self.h, i, C.byref(at))
+            out.append((name, float(at.value), ms))
         return out
 
     def imad_peak(self, reps=5):

@@ -142,13 +142,30 @@ def test_msm_window_override(ctx, window):
     n = 4000
     bases, inf = orc.g1_fixed_base(orc.sha512_rng_fr(1 << 42, n))
     s = _scalar_mix(n, 31, "dense")
-    ctx.set_option("window", window)
-    try:
-        got, ginf = ctx.msm_g1(bases, inf, s)
-    finally:
-        ctx.set_option("window", 0)
     want, winf = orc.msm_g1(bases, inf, s)
-    assert ginf == winf and np.array_equal(got, want)
+    for reduce_1d in (0, 1):      # two-dimensional and running-sum bucket reductions
+        ctx.set_option("window", window)
+        ctx.set_option("reduce_1d", reduce_1d)
+        try:
+            got, ginf = ctx.msm_g1(bases, inf, s)
+        finally:
+            ctx.set_option("window", 0)
+            ctx.set_option("reduce_1d", 0)
+        assert ginf == winf and np.array_equal(got, want), reduce_1d
+
+
+def test_msm_g2_two_dimensional_reduction(ctx):
+    n = 3000
+    bases, inf = orc.g2_fixed_base(orc.sha512_rng_fr(1 << 44, n))
+    s = _scalar_mix(n, 32, "dense")
+    want, winf = orc.msm_g2(bases, inf, s)
+    for window in (12, 15):
+        ctx.set_option("window", window)
+        try:
+            got, ginf = ctx.msm_g2(bases, inf, s)
+        finally:
+            ctx.set_option("window", 0)
+        assert ginf == winf and np.array_equal(got, want), window
 
 
 def test_msm_large_in_the_exponent(ctx):
