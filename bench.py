@@ -32,6 +32,10 @@ MAC_PER_G1_POINT = 23936     # 16 windows x 11 modmul x 136 MA
 MAC_PER_G2_POINT = 63104     # 16 x 29 x 136
 BYTES_PER_G1_POINT = 96      # 64 B affine base + 32 B scalar
 BYTES_PER_G2_POINT = 160
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the accumulate kernel at 2^20 points, from the ncu --set full
+# capture summarised in profiles/r1_ncu_msm_accumulate_2p20_full.csv (window tables: 13 table points are read per scalar,
+# so the traffic is ~12x the canonical 96/160 B per point; HBM stays under 11 % busy)
+NCU_TRAFFIC_BYTES = {("G2", 20): 1.916516e9 + 0.203396e9, ("G1", 20): 1.872888e9 + 0.104280e9}
 
 
 # ----------------------------------------------------------------------------------------------- multi-rank helpers
@@ -106,6 +110,39 @@ def rand_scalars(n, seed):
     a = rng.integers(0, 1 << 63, size=(n, 4), dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=(n, 4), dtype=np.uint64)
     a[:, 3] &= np.uint64((1 << 60) - 1)
     return np.ascontiguousarray(a)
+
+
+# ----------------------------------------------------------------------------------------------- self-check
+Q_MOD = 21888242871839275222246405745257275088696311157297823662689037894645226208583
+
+
+def _ints(a):
+    a = np.asarray(a, np.uint64).reshape(-1, 4).astype(object)
+    return a[:, 0] | (a[:, 1] << 64) | (a[:, 2] << 128) | (a[:, 3] << 192)
+
+
+def verify_in_the_exponent(eb, ctx, key, witness, proof, dims):
+    """The synthetic key's bases are k_i * G with known k_i, so the proof has a closed form in the exponent:
+    A = (alpha + sum w_i kA_i) G1, B = (beta + sum w_i kB_i) G2, C = (sum h_j kH_j + sum w_l kL_l) G1.  The three
+    expected points come from the fixed-base double-and-add kernel, which shares nothing with the MSM/NTT path."""
+    from ethsnarks_b200.host import R_MOD, MONT_R, ints_to_limbs
+    rinv = pow(MONT_R, -1, R_MOD)
+    std = lambda a: (_ints(a) * rinv) % R_MOD                       # Montgomery limbs -> integers
+    nv, ni, m = dims["nv"], dims["ni"], dims["m"]
+    w = std(witness)
+    h = std(key.h_poly(witness))[:m - 1]
+    kA, kB, kH, kL = (std(rand_scalars(n, seed)) for n, seed in ((nv + 1, 101), (nv + 1, 102), (m - 1, 103), (nv - ni, 104)))
+    c1, c2 = std(rand_scalars(3, 105)), std(rand_scalars(2, 106))
+    eA = (int(c1[0]) + int(np.dot(w, kA))) % R_MOD
+    eB = (int(c2[0]) + int(np.dot(w, kB))) % R_MOD
+    eC = (int(np.dot(h, kH)) + int(np.dot(w[ni + 1:], kL))) % R_MOD
+    mont = lambda e: ints_to_limbs([(e * MONT_R) % R_MOD])
+    ok = True
+    for group, e, got in ((1, eA, proof[0]), (2, eB, proof[1]), (1, eC, proof[2])):
+        want = eb.Bases(ctx, group, scalars=mont(e)).download()[0][0]           # Montgomery affine
+        got_m = ints_to_limbs([(int(x) * MONT_R) % Q_MOD for x in _ints(got)]).reshape(-1)
+        ok = ok and bool(np.array_equal(np.asarray(want).reshape(-1), got_m))
+    return ok
 
 
 # ----------------------------------------------------------------------------------------------- workload
@@ -242,7 +279,7 @@ def run_ours(args):
     # sharded 1/N per GPU (the north-star's MSM split; strong scaling, it shortens the latency of ONE proof)
     sharded = None
     if world > 1 and args.mode == "both":
-        skey, switness, _ = build_workload(eb, ctx, args.log_m, rank, world)
+        skey, switness, sdims = build_workload(eb, ctx, args.log_m, rank, world)
         sw_dev = torch.from_numpy(switness.view(np.int64)).to(dev)
 
         def sstep():
@@ -254,6 +291,13 @@ def run_ours(args):
         sms, _ = timed_steps(sstep, args.steps)
         sharded = {"scaling": "strong", "parallelism": "key sharded 1/%d per GPU, 35x8 B partial sums all-gathered over NCCL" % world,
                    "latency_ms": sms / args.steps, "proofs_per_sec": args.steps / (sms * 1e-3)}
+        if args.verify:
+            sproof = sstep()
+            torch.cuda.synchronize()
+            if rank == 0:
+                sharded["verified_in_the_exponent"] = verify_in_the_exponent(eb, ctx, skey, switness, sproof, sdims)
+                if not sharded["verified_in_the_exponent"]:
+                    raise SystemExit("bench.py: the sharded proof does not match its closed form in the exponent")
         del skey, sw_dev
         torch.cuda.synchronize()
 
@@ -290,6 +334,14 @@ def run_ours(args):
     ctx.set_option("overlap", 1)
     clocks = sampler.stop() if rank == 0 else None
 
+    verified = None
+    if args.verify:
+        proof = step(w_dev.data_ptr())
+        torch.cuda.synchronize()
+        if rank == 0:
+            verified = verify_in_the_exponent(eb, ctx, key, witness, proof, dims)
+            if not verified:
+                raise SystemExit("bench.py: the proof does not match its closed form in the exponent")
     proofs = args.steps * (1 if (shard or world == 1) else world)
     value = proofs / (ms_dev * 1e-3)
     e2e = proofs / (ms_e2e * 1e-3)
@@ -331,7 +383,8 @@ def run_ours(args):
     if dom:
         kd = kernels[dom]
         roofline = {"bound": "imad", "kernel": kd["kernel"] + " (%s query)" % dom, "achieved": kd["tmac_s"], "peak": imad_peak / 1e12,
-                    "unit": "TMAC/s", "frac": kd["frac_imad"], "traffic": None,
+                    "unit": "TMAC/s", "frac": kd["frac_imad"],
+                    "traffic": NCU_TRAFFIC_BYTES.get(("G2" if dom == "B_g2" else "G1", args.log_m)) if world == 1 or not shard else None,
                     "peak_source": "b200_imad_peak microbenchmark (IMAD.WIDE.U32, all SMs), measured in this run",
                     "hbm": {"achieved": kd["gb_s"], "peak": hbm_peak, "unit": "GB/s", "frac": kd["gb_s"] / hbm_peak,
                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
@@ -355,7 +408,7 @@ def run_ours(args):
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "phases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" not in k},
         "msm_subphases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" in k},
-        "msm_kernels": kernels,
+        "msm_kernels": kernels, "verified_in_the_exponent": verified,
     }
     if sharded:
         line["sharded"] = sharded
@@ -378,6 +431,7 @@ def main():
     ap.add_argument("--mode", default="both", choices=["both", "shard", "replicas"])
     ap.add_argument("--cpu-sample-log-m", type=int, default=17)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--verify", type=int, default=1, help="check one proof against its closed form in the exponent (untimed)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
