@@ -62,6 +62,9 @@ typedef const __mpz_struct* mpz_srcptr;
 #define mpz_cmp __gmpz_cmp
 #define mpz_cmp_ui __gmpz_cmp_ui
 #define mpz_sizeinbase __gmpz_sizeinbase
+#define mpz_import __gmpz_import
+#define mpz_jacobi __gmpz_jacobi
+#define mpz_export __gmpz_export
 #define gmp_printf __gmp_printf
 
 void __gmpn_copyi(mp_ptr, mp_srcptr, mp_size_t);
@@ -86,6 +89,9 @@ size_t __gmpn_get_str(unsigned char*, int, mp_ptr, mp_size_t);
 mp_size_t __gmpn_gcdext(mp_ptr, mp_ptr, mp_size_t*, mp_ptr, mp_size_t, mp_ptr, mp_size_t);
 void __gmpn_tdiv_qr(mp_ptr, mp_ptr, mp_size_t, mp_srcptr, mp_size_t, mp_srcptr, mp_size_t);
 void __gmpz_init(mpz_ptr);
+int __gmpz_jacobi(mpz_srcptr, mpz_srcptr);
+void __gmpz_import(mpz_ptr, size_t, int, size_t, int, size_t, const void*);
+void* __gmpz_export(void*, size_t*, int, size_t, int, size_t, mpz_srcptr);
 void __gmpz_init_set(mpz_ptr, mpz_srcptr);
 void __gmpz_init_set_ui(mpz_ptr, unsigned long);
 int __gmpz_init_set_str(mpz_ptr, const char*, int);

@@ -45,5 +45,30 @@ def main():
         json.dump(out, fh, indent=1, sort_keys=True)
 
 
+REFERENCE_CIRCUITS = {
+    "sha256": "BASELINE configs[1]: sha256_full_gadget_512 on sha256('test')||sha256('test') (src/test/test_sha256_full_gadget.cpp:30-99)",
+    "mimc_merkle": "BASELINE configs[0]: merkle_path_authenticator<MiMC_e7_hash_gadget> depth 29 (src/gadgets/merkle_tree.hpp:70-192), "
+                   "after reproducing the depth-1 known answer of src/test/test_merkle_tree.cpp:56-62",
+    "eddsa": "BASELINE configs[2]: jubjub::EdDSA (Pedersen-hashed message) on the known signature of 'abc' "
+             "(src/test/jubjub/test_jubjub_eddsa.cpp:44-62)",
+}
+
+
+def make_reference_circuit_goldens():
+    """tests/golden/circuit_<name>.json: circuits built by the reference's own gadget code (oracle/_ref/circuit_dump, compiled
+    from /root/reference by oracle/ref/Makefile), proved by the oracle under the seeded key; tests/test_oracle.py checks that
+    the reference prover binary returns the same proofs."""
+    import orc_ref
+    for name, what in REFERENCE_CIRCUITS.items():
+        circ, w, out = orc_ref.reference_circuit(name)
+        key = orc.Key(circ)
+        proof = key.prove(w)
+        g = {"circuit": what, "dump_stdout": out, "constraints": circ.nc, "variables": circ.nv, "inputs": circ.ni, "m": circ.m,
+             "key_seed_base": 1 << 32, "proof_json": orc.proof_json(proof, w[1:1 + circ.ni]),
+             "witness_sha256": hashlib.sha256(np.ascontiguousarray(w).tobytes()).hexdigest()}
+        json.dump(g, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "circuit_%s.json" % name), "w"), indent=1)
+
+
 if __name__ == "__main__":
     main()
+    make_reference_circuit_goldens()

@@ -220,6 +220,21 @@ class Circuit:
         return Circuit(lib().orc_synth_field(C.c_uint64(nc), C.c_uint64(ni), C.c_uint64(seed_a), C.c_uint64(seed_b)))
 
     @staticmethod
+    def from_csr(nc, ni, nv, mats, coeffs):
+        """mats: three (row_ptr u64, col u32, coeff_idx u32); coeffs: (n, 4) Montgomery"""
+        args = []
+        keep = []
+        for rp, col, ci in mats:
+            rp = np.ascontiguousarray(rp, dtype=np.uint64); col = np.ascontiguousarray(col, dtype=np.uint32)
+            ci = np.ascontiguousarray(ci, dtype=np.uint32)
+            keep += [rp, col, ci]
+            args += [p64(rp), p32(col), p32(ci)]
+        coeffs = np.ascontiguousarray(coeffs, dtype=np.uint64)
+        lib().orc_circuit_new.restype = C.c_void_p
+        return Circuit(lib().orc_circuit_new(C.c_uint64(nc), C.c_uint64(ni), C.c_uint64(nv), *args, p64(coeffs),
+                                              C.c_uint64(coeffs.shape[0])))
+
+    @staticmethod
     def synth_binary(nc, ni, seed=1):
         return Circuit(lib().orc_synth_binary(C.c_uint64(nc), C.c_uint64(ni), C.c_uint64(seed)))
 

@@ -12,8 +12,36 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "ref_prove")
 
 
+DUMP_BIN = os.path.join(ROOT, "oracle", "_ref", "circuit_dump")
+
+
 def available():
     return os.path.exists(REF_BIN)
+
+
+def dump_available():
+    return os.path.exists(DUMP_BIN)
+
+
+def reference_circuit(name):
+    """Builds `name` ("sha256") with the reference's own gadget code (oracle/_ref/circuit_dump) and returns
+    (oracle Circuit, witness (nv+1, 4) Montgomery, the dumper's stdout)."""
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "circuit.bin")
+        res = subprocess.run([DUMP_BIN, name, path], check=True, capture_output=True, text=True)
+        raw = open(path, "rb").read()
+    nc, ni, nv, ncoef = struct.unpack("<QQQQ", raw[:32])
+    off = 32
+    coeffs = np.frombuffer(raw, np.uint64, ncoef * 4, off).reshape(ncoef, 4).copy(); off += 32 * ncoef
+    mats = []
+    for _ in range(3):
+        nnz = struct.unpack("<Q", raw[off:off + 8])[0]; off += 8
+        rp = np.frombuffer(raw, np.uint64, nc + 1, off).copy(); off += 8 * (nc + 1)
+        col = np.frombuffer(raw, np.uint32, nnz, off).copy(); off += 4 * nnz
+        ci = np.frombuffer(raw, np.uint32, nnz, off).copy(); off += 4 * nnz
+        mats.append((rp, col, ci))
+    w = np.frombuffer(raw, np.uint64, (nv + 1) * 4, off).reshape(nv + 1, 4).copy()
+    return orc.Circuit.from_csr(nc, ni, nv, mats, coeffs), w, res.stdout
 
 
 def write_problem(path, circ, w, pk_alt_nozk_bytes):

@@ -1,6 +1,7 @@
 """GPU parity tests: every call goes through the C ABI (libb200snark.so) and is compared bit-for-bit with the CPU oracle
 on the same seeded inputs.  Run on the B200 box: python -m pytest tests -m gpu."""
 import json
+import os
 import numpy as np
 import pytest
 import orc
@@ -325,4 +326,30 @@ def test_window_tables_on_and_off_give_the_same_results(ctx):
         got = pk.prove(w)
         for g, e in zip(got, want):
             assert np.array_equal(np.asarray(g), np.asarray(e)), pre
+        pk.free()
+
+
+@pytest.mark.parametrize("name", ["sha256", "mimc_merkle", "eddsa"])
+def test_reference_gadget_circuits(ctx, name):
+    """BASELINE.json configs[0..2]: circuits built by the reference's own gadget code (oracle/_ref/circuit_dump; SHA256 full,
+    MiMC Merkle depth 29, Baby Jubjub EdDSA — real, 0/1-heavy witnesses): witness map, H and proof from the GPU equal the
+    oracle's and the committed golden proof that the reference prover binary reproduces (tests/test_oracle.py)."""
+    import orc_ref
+    if not orc_ref.dump_available():
+        pytest.skip("oracle/_ref/circuit_dump not built")
+    circ, w, out = orc_ref.reference_circuit(name)
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "circuit_%s.json" % name)))
+    assert out == g["dump_stdout"]
+    key = orc.Key(circ)
+    want = key.prove(w)
+    for fo, fg in ((orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK), (orc.FMT_ALT_FULL, eb.FMT_ALT_FULL)):
+        pk = _load(ctx, circ, key, fo, fg)
+        a, b, c = pk.witness_eval(w)
+        h_want, ev = circ.h_poly(w, evals=True)
+        assert np.array_equal(a, ev[0][:circ.m]) and np.array_equal(b, ev[1][:circ.m]) and np.array_equal(c, ev[2][:circ.m])
+        assert np.array_equal(pk.h_poly(w), h_want[:circ.m])
+        got = pk.prove(w)
+        for x, y in zip(got, want):
+            assert np.array_equal(np.asarray(x), np.asarray(y))
+        assert eb.proof_to_json(got, eb.host.fr_from_mont(w[1:1 + circ.ni])) == g["proof_json"]
         pk.free()

@@ -8,6 +8,10 @@ import numpy as np
 import kat
 import orc
 import pairing
+import pytest
+import orc_ref
+
+HERE = os.path.dirname(os.path.abspath(__file__))
 
 GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))
 
@@ -150,3 +154,33 @@ def test_reference_build_reads_the_oracle_key_bytes_and_matches_golden():
     c = orc.Circuit.synth_field(30, 3); w = c.witness(); k = orc.Key(c)
     proof, _, _ = orc_ref.prove(c, w, k, threads=1)
     assert orc.proof_json(proof, w[1:1 + c.ni]) == GOLD["circuits"]["field_30_3"]["proof_json"]
+
+
+@pytest.mark.skipif(not (orc_ref.available() and orc_ref.dump_available()), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("name", ["sha256", "mimc_merkle", "eddsa"])
+def test_reference_gadget_circuits_oracle_equals_reference_prover(name):
+    """BASELINE.json configs[0..2]: circuits built by the reference's OWN gadget code (oracle/_ref/circuit_dump, compiled from
+    the reference sources): sha256_full_gadget_512 (digest = the KAT of test_sha256_full_gadget.cpp:48-52), the depth-29 MiMC
+    Merkle authenticator (after reproducing the depth-1 root of test_merkle_tree.cpp:56-62) and Baby Jubjub EdDSA on the
+    known signature of test_jubjub_eddsa.cpp:44-62.  The oracle and the reference prover binary prove the same R1CS + real
+    witness to identical points and H; the proof passes the restated reference verifier."""
+    circ, w, out = orc_ref.reference_circuit(name)
+    g = json.load(open(os.path.join(HERE, "golden", "circuit_%s.json" % name)))
+    assert out == g["dump_stdout"] and "satisfied 1" in out
+    if name == "sha256":
+        assert "digest D294F6E585874FE640BE4CE636E6EF9E3ADC27620AA3221FDCF5C0A7C11C6F67" in out
+    if name == "mimc_merkle":
+        assert "merkle KAT (test_merkle_tree.cpp:56-62) reproduced" in out
+    assert (circ.nc, circ.nv, circ.ni, circ.m) == (g["constraints"], g["variables"], g["inputs"], g["m"])
+    assert circ.is_satisfied(w)
+    assert hashlib.sha256(np.ascontiguousarray(w).tobytes()).hexdigest() == g["witness_sha256"]
+    key = orc.Key(circ)
+    want = key.prove(w)
+    assert key.check_in_exponent(w, want) == 0
+    got, h_ref, _ = orc_ref.prove(circ, w, key, threads=1)
+    for a, b in zip(got[:3], want[:3]):
+        assert np.array_equal(np.asarray(a), np.asarray(b))
+    assert np.array_equal(h_ref[:circ.m], circ.h_poly(w)[:circ.m])
+    pj = orc.proof_json(want, w[1:1 + circ.ni])
+    assert pj == g["proof_json"]
+    assert pairing.groth16_verify(json.loads(key.vk_json()), json.loads(pj))
