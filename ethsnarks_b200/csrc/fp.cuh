@@ -30,6 +30,10 @@ struct FrParams {
         constexpr uint32_t m[8] = {0xae216da7u, 0x1bb8e645u, 0xe35c59e3u, 0x53fe3ab1u, 0x53bb8085u, 0x8c49833du, 0x7f4e44a5u, 0x0216d0b1u};
         return m[i];
     }
+    static __host__ __device__ constexpr uint32_t r3(int i) {    // R^3 mod r
+        constexpr uint32_t m[8] = {0xb4bf0040u, 0x5e94d8e1u, 0x1cfbb6b8u, 0x2a489cbeu, 0xa19fcfedu, 0x893cc664u, 0x7fcc657cu, 0x0cf8594bu};
+        return m[i];
+    }
     static constexpr uint32_t INV = 0xefffffffu;   // -r^{-1} mod 2^32
 };
 
@@ -45,6 +49,10 @@ struct FqParams {
     }
     static __host__ __device__ constexpr uint32_t r2(int i) {
         constexpr uint32_t m[8] = {0x538afa89u, 0xf32cfc5bu, 0xd44501fbu, 0xb5e71911u, 0x0a417ff6u, 0x47ab1effu, 0xcab8351fu, 0x06d89f71u};
+        return m[i];
+    }
+    static __host__ __device__ constexpr uint32_t r3(int i) {    // R^3 mod q
+        constexpr uint32_t m[8] = {0xda1530dfu, 0xb1cd6dafu, 0xa7283db6u, 0x62f210e6u, 0x0ada0afbu, 0xef7f0b0cu, 0x2d592544u, 0x20fd6e90u};
         return m[i];
     }
     static constexpr uint32_t INV = 0xe4866389u;
@@ -180,28 +188,29 @@ struct __align__(16) Fp {
     B200_DEV Fp neg() const { return is_zero() ? *this : (zero() - *this); }
     B200_DEV Fp dbl() const { return *this + *this; }
 
-    // Montgomery product a*b*R^-1 mod p, fully reduced.
-    friend B200_DEV Fp operator*(const Fp& a, const Fp& b) {
-        uint32_t E[8], O[8];
-        // row 0: E = a_even (x) b0, O = a_odd (x) b0 (O's limb k has weight 2^(32(k+1)))
+    // Montgomery product a*b*R^-1 mod p, fully reduced: CIOS, one row per limb of b, on two accumulators E / O holding the
+    // even- and odd-aligned partial products (so that every mad.lo/mad.hi pair is one IMAD.WIDE).
+    static B200_DEV void mont_row0(uint32_t* E, uint32_t* O, const Fp& a, uint32_t b0) {
+        // E = a_even (x) b0, O = a_odd (x) b0 (O's limb k has weight 2^(32(k+1)))
         _Pragma("unroll") for (int j = 0; j < 8; j += 2) {
-            uint64_t te = (uint64_t)a.v[j] * b.v[0], to = (uint64_t)a.v[j + 1] * b.v[0];
+            uint64_t te = (uint64_t)a.v[j] * b0, to = (uint64_t)a.v[j + 1] * b0;
             E[j] = (uint32_t)te; E[j + 1] = (uint32_t)(te >> 32);
             O[j] = (uint32_t)to; O[j + 1] = (uint32_t)(to >> 32);
         }
         uint32_t m = E[0] * P::INV;
         chain_mad(O, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
         chain_mad_carry(E, O[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
-        _Pragma("unroll") for (int i = 1; i < 8; ++i) {
-            uint32_t* X = (i & 1) ? O : E;   // even-aligned role this row
-            uint32_t* Y = (i & 1) ? E : O;   // odd-aligned role (holds last row's even array, limb 0 == 0)
-            chain_shift_mad(Y, X[0], a.v[1], a.v[3], a.v[5], a.v[7], b.v[i]);
-            chain_mad_carry(X, Y[7], a.v[0], a.v[2], a.v[4], a.v[6], b.v[i]);
-            m = X[0] * P::INV;
-            chain_mad(Y, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
-            chain_mad_carry(X, Y[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
-        }
-        // after row 7: X = O, Y = E; result = Y + (X >> 32)
+    }
+    // X: even-aligned role this row, Y: odd-aligned role (holds last row's even array, limb 0 == 0)
+    static B200_DEV void mont_row(uint32_t* X, uint32_t* Y, const Fp& a, uint32_t bi) {
+        chain_shift_mad(Y, X[0], a.v[1], a.v[3], a.v[5], a.v[7], bi);
+        chain_mad_carry(X, Y[7], a.v[0], a.v[2], a.v[4], a.v[6], bi);
+        uint32_t m = X[0] * P::INV;
+        chain_mad(Y, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+        chain_mad_carry(X, Y[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+    }
+    // after row 7: X = O, Y = E; result = Y + (X >> 32)
+    static B200_DEV Fp mont_final(const uint32_t* E, const uint32_t* O) {
         Fp r;
         asm("add.cc.u32 %0, %8, %16;\n\t"
             "addc.cc.u32 %1, %9, %17;\n\t"
@@ -216,6 +225,25 @@ struct __align__(16) Fp {
               "r"(O[1]), "r"(O[2]), "r"(O[3]), "r"(O[4]), "r"(O[5]), "r"(O[6]), "r"(O[7]));
         r.reduce_once();
         return r;
+    }
+    friend B200_DEV Fp operator*(const Fp& a, const Fp& b) {
+        uint32_t E[8], O[8];
+        mont_row0(E, O, a, b.v[0]);
+        _Pragma("unroll") for (int i = 1; i < 8; ++i) mont_row((i & 1) ? O : E, (i & 1) ? E : O, a, b.v[i]);
+        return mont_final(E, O);
+    }
+    // two independent products with their rows interleaved: two carry chains in flight per thread, for kernels whose
+    // register footprint leaves too few warps per scheduler to hide the IMAD.WIDE issue latency (G2)
+    static B200_DEV void mul2(const Fp& a, const Fp& b, const Fp& c, const Fp& d, Fp& ab, Fp& cd) {
+        uint32_t E0[8], O0[8], E1[8], O1[8];
+        mont_row0(E0, O0, a, b.v[0]);
+        mont_row0(E1, O1, c, d.v[0]);
+        _Pragma("unroll") for (int i = 1; i < 8; ++i) {
+            mont_row((i & 1) ? O0 : E0, (i & 1) ? E0 : O0, a, b.v[i]);
+            mont_row((i & 1) ? O1 : E1, (i & 1) ? E1 : O1, c, d.v[i]);
+        }
+        ab = mont_final(E0, O0);
+        cd = mont_final(E1, O1);
     }
     B200_DEV Fp sqr() const { return (*this) * (*this); }
 
@@ -232,6 +260,38 @@ struct __align__(16) Fp {
             if ((e >> i) & 1) r = r * (*this);
         }
         return r;
+    }
+    // Binary extended Euclid (the reference's Fp_model::inverse is the same algorithm family, fp.tcc:642-692): integer
+    // adds, subs and shifts only - no multiplier - so one thread can invert while the other warps keep the IMAD pipe.
+    // Input and output in Montgomery form; 0 -> 0.  (x R)^-1 = x^-1 R^-1, one Montgomery product with R^3 gives x^-1 R.
+    B200_DEV Fp inv_binary() const {
+        if (is_zero()) return *this;
+        uint32_t u[8], w[8], b[8], c[8];
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) { u[i] = v[i]; w[i] = P::mod(i); b[i] = 0; c[i] = 0; }
+        b[0] = 1;
+        auto is_one = [](const uint32_t* x) { uint32_t o = x[0] ^ 1u; _Pragma("unroll") for (int i = 1; i < 8; ++i) o |= x[i]; return o == 0; };
+        auto shr1 = [](uint32_t* x) { _Pragma("unroll") for (int i = 0; i < 7; ++i) x[i] = (x[i] >> 1) | (x[i + 1] << 31); x[7] >>= 1; };
+        auto add_mod_p = [](uint32_t* x) { uint64_t cy = 0; _Pragma("unroll") for (int i = 0; i < 8; ++i) { cy += (uint64_t)x[i] + P::mod(i); x[i] = (uint32_t)cy; cy >>= 32; } };
+        auto geq = [](const uint32_t* x, const uint32_t* y) {   // x >= y
+            _Pragma("unroll") for (int i = 7; i >= 0; --i) { if (x[i] != y[i]) return x[i] > y[i]; }
+            return true;
+        };
+        auto sub = [](uint32_t* x, const uint32_t* y) {          // x -= y, returns borrow
+            int64_t bw = 0;
+            _Pragma("unroll") for (int i = 0; i < 8; ++i) { bw += (int64_t)x[i] - (int64_t)y[i]; x[i] = (uint32_t)bw; bw >>= 32; }
+            return bw != 0;
+        };
+        auto halve = [&](uint32_t* x) { if (x[0] & 1u) add_mod_p(x); shr1(x); };   // x/2 mod p (x + p < 2^255)
+        while (!is_one(u) && !is_one(w)) {
+            while (!(u[0] & 1u)) { shr1(u); halve(b); }
+            while (!(w[0] & 1u)) { shr1(w); halve(c); }
+            if (geq(u, w)) { sub(u, w); if (sub(b, c)) add_mod_p(b); }
+            else { sub(w, u); if (sub(c, b)) add_mod_p(c); }
+        }
+        Fp y, r3;
+        const uint32_t* res = is_one(u) ? b : c;
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) { y.v[i] = res[i]; r3.v[i] = P::r3(i); }
+        return y * r3;
     }
     // Fermat inverse this^(p-2); 0 -> 0.  (The reference uses binary extended GCD, fp.tcc:642-692; same value.)
     B200_DEV Fp inv() const {
@@ -273,17 +333,35 @@ struct Fq2 {
         return x * y;
 #endif
     }
+#ifndef B200_FQ2_MUL2
+#define B200_FQ2_MUL2 0     // 1: pairs of Fq products inside Fq2 go through Fq::mul2 (rows interleaved)
+#endif
     friend B200_DEV Fq2 operator*(const Fq2& x, const Fq2& y) {   // Karatsuba, 3 Fq products
+#if B200_FQ2_MUL2
+        Fq aa, bb;
+        Fq::mul2(x.a, y.a, x.b, y.b, aa, bb);
+#else
         Fq aa = fqmul(x.a, y.a), bb = fqmul(x.b, y.b);
+#endif
         Fq m = fqmul(x.a + x.b, y.a + y.b);
         return Fq2{aa - bb, m - aa - bb};
     }
     B200_DEV Fq2 sqr() const {   // complex squaring, 2 Fq products
+#if B200_FQ2_MUL2
+        Fq ab, d;
+        Fq::mul2(a, b, a + b, a - b, ab, d);
+        return Fq2{d, ab.dbl()};
+#else
         Fq ab = fqmul(a, b);
         return Fq2{fqmul(a + b, a - b), ab.dbl()};
+#endif
     }
     B200_DEV Fq2 inv() const {
         Fq n = (a.sqr() + b.sqr()).inv();
+        return Fq2{a * n, (b * n).neg()};
+    }
+    B200_DEV Fq2 inv_binary() const {   // conjugate over the norm, the norm inverted without the multiplier
+        Fq n = (a.sqr() + b.sqr()).inv_binary();
         return Fq2{a * n, (b * n).neg()};
     }
 };

@@ -24,6 +24,8 @@ struct b200_ctx {
     unsigned long long launches = 0;   // kernels launched by this library since init
     int window_override = 0;           // 0 = cost model
     int chunk_override = 0;            // 0 = auto
+    int affine_rounds = 0;             // batched-affine pre-reduction rounds before the XYZZ accumulate (experimental:
+                                       // correct but slower than XYZZ alone on B200); -1 = by run length
     int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one
     int precompute = 1;                // build fixed-base window tables for resident keys / base sets
     // lanes: extra streams so the independent MSMs of one prove overlap (the latency-bound reduction tail of one MSM

@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(128, G::kAccMinBlocks) msm_accumulate(const ui
             acc = Pt::inf();
             cur = k;
         }
-        const uint32_t v = vals[i];
+        const uint32_t v = vals ? vals[i] : (uint32_t)i;     // no value list: the points are already in list order
         Aff p = bases[v & 0x7fffffffu];
         if (v >> 31) p.y = p.y.neg();
         acc.add_mixed(p);

@@ -147,11 +147,28 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     msm_offsets<<<(p.nb + 1 + 255) / 256, 256, 0, st>>>(skeys, p.pairs, p.nb, offsets);
     ctx->launches++;
     ctx->t_end();
+    // batched-affine pre-reduction: R rounds leave runs 2^R times shorter for the XYZZ accumulate
+    int rounds = ctx->affine_rounds;
+    if (rounds < 0) {
+        const double avg_run = (double)p.pairs / (double)p.nb;
+        rounds = 0;
+        while (rounds < 4 && avg_run >= (double)(8 << rounds)) ++rounds;      // keep >= ~4 per run for the accumulate
+    }
+    const uint32_t* akeys = skeys;
+    const uint32_t* avals = svals;
+    const void* abases = d_bases;
+    const uint64_t* aoff = offsets;
+    if (rounds > 0) {
+        ctx->t_begin("msm.affine");
+        launch_affine_rounds<G>(ctx, st, p, rounds, skeys, svals, d_bases, offsets, &akeys, &abases, &aoff);
+        avals = nullptr;
+        ctx->t_end();
+    }
     ctx->t_begin("msm.accumulate");
-    launch_accumulate<G>(ctx, st, p, skeys, svals, offsets, d_bases, buckets, pfirst, plast);
+    launch_accumulate<G>(ctx, st, p, akeys, avals, aoff, abases, buckets, pfirst, plast);
     ctx->t_end();
     ctx->t_begin("msm.finalize");
-    launch_finalize<G>(ctx, st, p, offsets, buckets, pfirst, plast, big, big_cap);
+    launch_finalize<G>(ctx, st, p, aoff, buckets, pfirst, plast, big, big_cap);
     ctx->t_end();
     ctx->t_begin("msm.reduce");
     launch_reduce<G>(ctx, st, p, buckets, seg, win, d_out);

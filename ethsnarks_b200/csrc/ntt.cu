@@ -276,6 +276,7 @@ __global__ void field_op_kernel(int op, const F* __restrict__ a, const F* __rest
         case 4: r = x.from_mont(); break;
         case 5: r = x.inv(); break;
         case 6: r = x.sqr(); break;
+        case 8: r = x.inv_binary(); break;
         default: r = x.neg(); break;
     }
     out[i] = r;

@@ -29,11 +29,13 @@ def main():
     ap.add_argument("--tables", type=int, default=1)
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--groups", default="1,2")
+    ap.add_argument("--affine-rounds", type=int, default=-1)
     args = ap.parse_args()
     ctx = eb.Context(0)
     peak = ctx.imad_peak(5)
     if args.chunk:
         ctx.set_option("chunk", args.chunk)
+    ctx.set_option("affine_rounds", args.affine_rounds)
     if not args.no_check:
         import orc
     for group in [int(g) for g in args.groups.split(",")]:
@@ -62,7 +64,7 @@ def main():
             mac = (MAC_PER_G1_POINT if group == 1 else MAC_PER_G2_POINT) * n
             print(json.dumps({"group": "G%d" % group, "log_n": logn, "ms": ms, "mpoints_per_s": n / ms / 1e3,
                               "tmac_s_canonical": mac / (ms * 1e-3) / 1e12, "frac_of_imad_peak": mac / (ms * 1e-3) / peak,
-                              "imad_peak_tmac_s": peak / 1e12, "in_exponent_ok": ok, "tables": bool(args.tables), "chunk": args.chunk,
+                              "imad_peak_tmac_s": peak / 1e12, "in_exponent_ok": ok, "tables": bool(args.tables), "chunk": args.chunk, "affine_rounds": args.affine_rounds,
                               "phases_ms": {kk: round(float(np.min(v)), 4) for kk, v in sub.items()}}), flush=True)
             bases.free()
             del s_dev
