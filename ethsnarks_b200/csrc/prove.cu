@@ -25,6 +25,7 @@ struct b200_key {
     b200_ctx* ctx = nullptr;
     bool full = false;          // has the B query in G1 (r,s mode possible)
     bool owns_bases = true;
+    bool attached = false;      // a second prove slot on a resident key: shares every read-only buffer, owns only d_w/d_a/d_b/d_c
     int rank = 0, world = 1;
     uint64_t domain_size = 0;   // num_variables + 1
     uint64_t nA = 0, nB = 0, nH = 0, nL = 0;   // entries held by this rank
@@ -125,6 +126,11 @@ inline uint32_t bitrev32(uint32_t x, uint32_t bits) {
 
 void key_release(b200_key* k) {
     if (!k) return;
+    if (k->attached) {
+        cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
+        delete k;
+        return;
+    }
     if (k->owns_bases) { cudaFree(k->A); cudaFree(k->B2); cudaFree(k->B1); cudaFree(k->L); }
     cudaFree(k->H);
     cudaFree(k->A_t); cudaFree(k->B2_t); cudaFree(k->B1_t); cudaFree(k->H_t); cudaFree(k->L_t);
@@ -302,6 +308,28 @@ int b200_key_set_shard(b200_key* k, int rank, int world, uint64_t L_lo) {
     if (!k || world < 1 || rank < 0 || rank >= world || k->has_circuit) return B200_ERR_ARG;
     k->rank = rank; k->world = world; k->L_lo = L_lo;
     return B200_OK;
+}
+
+int b200_key_attach(b200_key* key, b200_ctx* ctx, b200_key** out) {
+    if (!key || !ctx || !out) return B200_ERR_ARG;
+    if (!key->has_circuit) { ctx->last_error = "key_attach before circuit_load"; return B200_ERR_STATE; }
+    if (ctx->device != key->ctx->device) { ctx->last_error = "key_attach: the context is on another device"; return B200_ERR_ARG; }
+    return Guard{ctx}.run([&] {
+        std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(*key), key_release);
+        k->attached = true;
+        k->ctx = ctx;
+        k->H_host.clear();
+        k->d_w = k->d_a = k->d_b = k->d_c = nullptr;
+        B200_CUDA_CHECK(cudaMalloc(&k->d_w, (k->nv + 1) * 32));
+        B200_CUDA_CHECK(cudaMalloc(&k->d_a, k->m * 32));
+        B200_CUDA_CHECK(cudaMalloc(&k->d_b, k->m * 32));
+        B200_CUDA_CHECK(cudaMalloc(&k->d_c, k->m * 32));
+        B200_CUDA_CHECK(cudaMemset(k->d_a, 0, k->m * 32));
+        B200_CUDA_CHECK(cudaMemset(k->d_b, 0, k->m * 32));
+        B200_CUDA_CHECK(cudaMemset(k->d_c, 0, k->m * 32));
+        *out = k.release();
+        return (int)B200_OK;
+    });
 }
 
 void b200_key_free(b200_key* key) {

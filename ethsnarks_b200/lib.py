@@ -6,6 +6,7 @@ shared library is missing, or no CUDA device is present, construction fails loud
 """
 import ctypes as C
 import os
+import weakref
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -26,7 +27,7 @@ SYMBOLS = [
     "b200_g2_fixed_base", "b200_ntt", "b200_msm_g1", "b200_msm_g2", "b200_bases_upload", "b200_bases_generate",
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
-    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute",
+    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach",
 ]
 
 
@@ -78,6 +79,7 @@ class Context:
         if rc:
             raise B200Error(f"b200_init(device={device}) failed: {self.lib.b200_strerror(rc).decode()}")
         self.device = device
+        self._children = weakref.WeakSet()    # live Bases / ProvingKey objects: freed before the context goes away
 
     def check(self, rc, what):
         if rc:
@@ -85,6 +87,8 @@ class Context:
 
     def close(self):
         if self.h:
+            for child in sorted(self._children, key=lambda c: not getattr(c, "_attached", False)):   # attached slots first
+                child.free()
             self.lib.b200_shutdown(self.h)
             self.h = C.c_void_p()
 
@@ -205,6 +209,7 @@ class Bases:
             infp = _arr(inf, np.uint8).ctypes.data_as(u8p) if inf is not None else None
             ctx.check(ctx.lib.b200_bases_upload(ctx.h, group, _p64(xy), infp, C.c_size_t(n), C.byref(self.h)), "bases_upload")
         self.n = int(ctx.lib.b200_bases_count(self.h))
+        ctx._children.add(self)
 
     def precompute(self, window=0):
         self.ctx.check(self.ctx.lib.b200_bases_precompute(self.h, window), "bases_precompute")
@@ -231,9 +236,9 @@ class Bases:
         return out, oi.value
 
     def free(self):
-        if self.h:
+        if self.h and self.ctx.h:
             self.ctx.lib.b200_bases_free(self.h)
-            self.h = C.c_void_p()
+        self.h = C.c_void_p()
 
     def __del__(self):
         try:
@@ -248,6 +253,9 @@ class ProvingKey:
     def __init__(self, ctx, handle, keep=()):
         self.ctx, self.h, self._keep = ctx, handle, keep
         self._circuit_keep = None
+        self._attached = False
+        self._slots = weakref.WeakSet()       # prove slots attached to this key: freed before it
+        ctx._children.add(self)
 
     @staticmethod
     def load(ctx, pk_bytes, fmt=FMT_MCL_NOZK, rank=0, world=1):
@@ -267,6 +275,16 @@ class ProvingKey:
             bi.ctypes.data_as(u32p) if bi is not None else None, H.h, L.h, _p64(g1c), _p64(g2c), C.c_uint64(num_variables),
             C.c_uint64(num_inputs), C.byref(h)), "key_from_bases")
         return ProvingKey(ctx, h, keep=(A, B_g2, B_g1, H, L))
+
+    def attach(self, ctx):
+        """A second prove slot on this resident key, bound to another Context on the same device (pipelined proving)."""
+        h = C.c_void_p()
+        ctx.check(ctx.lib.b200_key_attach(self.h, ctx.h, C.byref(h)), "key_attach")
+        slot = ProvingKey(ctx, h, keep=(self,))
+        slot.m = self.m
+        slot._attached = True
+        self._slots.add(slot)
+        return slot
 
     def set_shard(self, rank, world, L_lo):
         self.ctx.check(self.ctx.lib.b200_key_set_shard(self.h, rank, world, C.c_uint64(L_lo)), "key_set_shard")
@@ -336,9 +354,11 @@ class ProvingKey:
         return A, B, Cc, inf
 
     def free(self):
-        if self.h:
+        for slot in list(self._slots):
+            slot.free()
+        if self.h and self.ctx.h:
             self.ctx.lib.b200_key_free(self.h)
-            self.h = C.c_void_p()
+        self.h = C.c_void_p()
 
     def __del__(self):
         try:

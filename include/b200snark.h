@@ -108,6 +108,11 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
 /* multi-GPU with b200_key_from_bases: declare that A / B_g2 / L hold this rank's slice (L starting at entry L_lo of the
  * full L query) and that H is the full query, to be sliced by rank at b200_circuit_load.  Call before circuit_load. */
 int b200_key_set_shard(b200_key* key, int rank, int world, uint64_t L_lo);
+/* A second prove slot on a resident key for pipelined proving (the reference's ProverContext reuse,
+ * r1cs_gg_ppzksnark_zok.hpp:279-291): shares every read-only device buffer of `key` (bases, window tables, circuit, domain)
+ * and owns only its witness / evaluation buffers, bound to another context (same device), so two proofs can be in flight
+ * from two host threads.  Free the slot before the key it was attached to. */
+int b200_key_attach(b200_key* key, b200_ctx* ctx, b200_key** out);
 void b200_key_free(b200_key* key);
 /* out[0..7]: domain_size (= num_variables + 1), |A|, |B|, |H|, |L| (this rank's counts), full(0/1), m, num_inputs */
 int b200_key_info(b200_key* key, uint64_t out[8]);

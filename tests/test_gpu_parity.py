@@ -386,3 +386,40 @@ def test_reference_gadget_circuits(ctx, name):
             assert np.array_equal(np.asarray(x), np.asarray(y))
         assert eb.proof_to_json(got, eb.host.fr_from_mont(w[1:1 + circ.ni])) == g["proof_json"]
         pk.free()
+
+
+def test_key_attach_second_prove_slot_and_handle_lifetimes(ctx):
+    """b200_key_attach: a second prove slot on a resident key, driven concurrently from another host thread on another
+    context, gives the same proofs; closing a context with live keys does not crash (children are freed first)."""
+    import threading
+    circ = orc.Circuit.synth_field(5000, 2, 7, 8)
+    w = circ.witness()
+    key = orc.Key(circ)
+    want = key.prove(w)
+    pk = _load(ctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
+    ctx2 = eb.Context(0)
+    slot = pk.attach(ctx2)
+    results = {}
+
+    def work(name, k):
+        results[name] = [k.prove(w) for _ in range(4)]
+    th = [threading.Thread(target=work, args=("a", pk)), threading.Thread(target=work, args=("b", slot))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for name in ("a", "b"):
+        for got in results[name]:
+            for g, e in zip(got, want):
+                assert np.array_equal(np.asarray(g), np.asarray(e)), name
+    ctx2.close()          # frees the attached slot first
+    assert not slot.h
+    got = pk.prove(w)     # the parent key is untouched
+    for g, e in zip(got, want):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    pk.free()
+    ctx3 = eb.Context(0)
+    orphan = _load(ctx3, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
+    ctx3.close()
+    assert not orphan.h
+    orphan.free()
