@@ -3,6 +3,7 @@
 #include "../../include/b200snark.h"
 #include "internal.hpp"
 #include <cstring>
+#include <cstdlib>
 #include <cstdio>
 #include <algorithm>
 #include <memory>
@@ -178,11 +179,14 @@ int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);   // numerically lower = higher priority
     auto prio = [&](int level) { return std::max(prio_hi, std::min(prio_lo, prio_lo - level)); };
-    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio(1)) != cudaSuccess) { delete c; return B200_ERR_CUDA; }
+    int lv[4] = {1, 2, 0, 0};                               // main, G2 lane, A lane, L lane
+    if (const char* e = getenv("B200_LANE_PRIO")) {         // tuning knob: four digits, e.g. "1211"
+        for (int i = 0; i < 4 && e[i] >= '0' && e[i] <= '9'; ++i) lv[i] = e[i] - '0';
+    }
+    if (const char* e = getenv("B200_G2_ACC_SMEM_KB")) c->g2_acc_smem = atoi(e) * 1024;
+    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio(lv[0])) != cudaSuccess) { delete c; return B200_ERR_CUDA; }
     c->lanes[0] = c->stream;
-    cudaStreamCreateWithPriority(&c->lanes[1], cudaStreamNonBlocking, prio(2));
-    cudaStreamCreateWithPriority(&c->lanes[2], cudaStreamNonBlocking, prio(0));
-    cudaStreamCreateWithPriority(&c->lanes[3], cudaStreamNonBlocking, prio(0));
+    for (int i = 1; i < 4; ++i) cudaStreamCreateWithPriority(&c->lanes[i], cudaStreamNonBlocking, prio(lv[i]));
     for (int i = 0; i < 4; ++i) cudaEventCreateWithFlags(&c->lane_done[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_witness, cudaEventDisableTiming);
     cudaDeviceProp prop;

@@ -26,6 +26,8 @@ struct b200_ctx {
     int chunk_override = 0;            // 0 = auto
     int affine_rounds = 0;             // batched-affine pre-reduction rounds before the XYZZ accumulate (experimental:
                                        // correct but slower than XYZZ alone on B200); -1 = by run length
+    int g2_acc_smem = 0;               // dynamic shared memory requested by msm_accumulate<G2> only to cap its blocks per SM,
+                                       // so that G1 accumulate blocks of the other lanes are co-resident with it
     int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one
     int precompute = 1;                // build fixed-base window tables for resident keys / base sets
     // lanes: extra streams so the independent MSMs of one prove overlap (the latency-bound reduction tail of one MSM

@@ -41,7 +41,12 @@ template <typename G>
 void launch_accumulate(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* skeys, const uint32_t* svals,
                        const uint64_t* offsets, const void* d_bases, void* buckets, void* pfirst, void* plast) {
     typedef typename G::Pt Pt;
-    msm_accumulate<G><<<(unsigned)((p.nchunks + 127) / 128), 128, 0, st>>>(skeys, svals, offsets, p.nb, p.L, (const typename G::Aff*)d_bases,
+    size_t smem = 0;
+    if (sizeof(Pt) > 128 && ctx->g2_acc_smem > 0) {
+        smem = (size_t)ctx->g2_acc_smem;
+        B200_CUDA_CHECK(cudaFuncSetAttribute(msm_accumulate<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    msm_accumulate<G><<<(unsigned)((p.nchunks + 127) / 128), 128, smem, st>>>(skeys, svals, offsets, p.nb, p.L, (const typename G::Aff*)d_bases,
                                                                             (Pt*)buckets, (Pt*)pfirst, (Pt*)plast);
     ctx->launches++;
 }

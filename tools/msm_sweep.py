@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--tables", type=int, default=1)
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--groups", default="1,2")
-    ap.add_argument("--affine-rounds", type=int, default=-1)
+    ap.add_argument("--affine-rounds", type=int, default=0)
     args = ap.parse_args()
     ctx = eb.Context(0)
     peak = ctx.imad_peak(5)
