@@ -183,13 +183,65 @@ void build_tables(b200_key* k) {
     B200_CUDA_CHECK(cudaStreamSynchronize(k->ctx->stream));
 }
 
+
+// ---- device-native key cache (B200_FMT_CACHE): the arrays exactly as they sit in HBM (affine Montgomery, (0,0) = infinity),
+// so a reload is a handful of large copies instead of a point-by-point parse of the reference's mixed ASCII/binary layout.
+//   "B2KC0001" | u64 full, domain_size, nA, nB, nH, nL | g1 consts 192 B | g2 consts 256 B | A_idx u32[nA] (+pad to 8 B) |
+//   B_idx u32[nB] (+pad) | A 64 B x nA | B_g2 128 B x nB | B_g1 64 B x nB (full keys) | H 64 B x nH (natural order) | L 64 B x nL
+const char KEY_CACHE_MAGIC[9] = "B2KC0001";
+inline size_t pad8(size_t n) { return (n + 7) & ~(size_t)7; }
+
+int key_load_cache(b200_ctx* ctx, const uint8_t* p, size_t len, int rank, int world, b200_key** out) {
+    if (len < 8 + 6 * 8 + 192 + 256 || memcmp(p, KEY_CACHE_MAGIC, 8) != 0) throw std::domain_error("key cache: bad magic or truncated header");
+    uint64_t hdr[6];
+    memcpy(hdr, p + 8, sizeof hdr);
+    const uint64_t full = hdr[0], ds = hdr[1], nA = hdr[2], nB = hdr[3], nH = hdr[4], nL = hdr[5];
+    if (full > 1) throw std::domain_error("key cache: bad header");
+    size_t off = 8 + sizeof hdr;
+    const uint8_t* c1 = p + off; off += 192;
+    const uint8_t* c2 = p + off; off += 256;
+    const size_t need = off + pad8(nA * 4) + pad8(nB * 4) + nA * 64 + nB * 128 + (full ? nB * 64 : 0) + nH * 64 + nL * 64;
+    if (nA > (1ull << 31) || nB > (1ull << 31) || nH > (1ull << 31) || nL > (1ull << 31) || len < need) throw std::domain_error("key cache: truncated");
+    const uint32_t* a_idx = (const uint32_t*)(p + off); off += pad8(nA * 4);
+    const uint32_t* b_idx = (const uint32_t*)(p + off); off += pad8(nB * 4);
+    const uint8_t* A = p + off; off += nA * 64;
+    const uint8_t* B2 = p + off; off += nB * 128;
+    const uint8_t* B1 = p + off; off += full ? nB * 64 : 0;
+    const uint8_t* H = p + off; off += nH * 64;
+    const uint8_t* L = p + off;
+    std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
+    k->ctx = ctx; k->rank = rank; k->world = world; k->full = full != 0; k->domain_size = ds;
+    k->consts_g1 = dev_upload_bytes(c1, 192);
+    k->consts_g2 = dev_upload_bytes(c2, 256);
+    uint64_t lo, hi;
+    shard_range(nA, rank, world, lo, hi);
+    for (uint64_t i = lo; i < hi; ++i) if (a_idx[i] >= ds) throw std::domain_error("key cache: A index out of range");
+    k->nA = hi - lo;
+    k->A_idx = (uint32_t*)dev_upload_bytes((const uint8_t*)(a_idx + lo), (hi - lo) * 4);
+    k->A = dev_upload_bytes(A + lo * 64, (hi - lo) * 64);
+    shard_range(nB, rank, world, lo, hi);
+    for (uint64_t i = lo; i < hi; ++i) if (b_idx[i] >= ds) throw std::domain_error("key cache: B index out of range");
+    k->nB = hi - lo;
+    k->B_idx = (uint32_t*)dev_upload_bytes((const uint8_t*)(b_idx + lo), (hi - lo) * 4);
+    k->B2 = dev_upload_bytes(B2 + lo * 128, (hi - lo) * 128);
+    if (k->full) k->B1 = dev_upload_bytes(B1 + lo * 64, (hi - lo) * 64);
+    k->H_total = nH;
+    k->H_host.assign(H, H + nH * 64);
+    shard_range(nL, rank, world, lo, hi);
+    k->L = dev_upload_bytes(L + lo * 64, (hi - lo) * 64);
+    k->nL = hi - lo; k->L_lo = lo;
+    *out = k.release();
+    return (int)B200_OK;
+}
+
 }  // namespace
 
 extern "C" {
 
 int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt, int rank, int world, b200_key** out) {
-    if (!ctx || !bytes || !out || fmt < 0 || fmt > 3 || world < 1 || rank < 0 || rank >= world) return B200_ERR_ARG;
+    if (!ctx || !bytes || !out || fmt < 0 || fmt > 4 || world < 1 || rank < 0 || rank >= world) return B200_ERR_ARG;
     *out = nullptr;
+    if (fmt == B200_FMT_CACHE) return Guard{ctx}.run([&] { return key_load_cache(ctx, (const uint8_t*)bytes, len, rank, world, out); });
     return Guard{ctx}.run([&] {
         std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
         k->ctx = ctx; k->rank = rank; k->world = world;
@@ -268,6 +320,40 @@ int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt,
         return (int)B200_OK;
     });
 }
+int b200_key_export(b200_key* k, void* buf, size_t cap, size_t* len_out) {
+    if (!k || !len_out) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (k->has_circuit || k->world != 1 || !k->owns_bases) {
+        ctx->last_error = "key_export: only a whole key loaded from bytes, before circuit_load";
+        return B200_ERR_STATE;
+    }
+    return Guard{ctx}.run([&] {
+        const uint64_t nH = k->H_total;
+        const size_t need = 8 + 6 * 8 + 192 + 256 + pad8(k->nA * 4) + pad8(k->nB * 4) + k->nA * 64 + k->nB * 128 +
+                            (k->full ? k->nB * 64 : 0) + nH * 64 + k->nL * 64;
+        *len_out = need;
+        if (!buf || cap < need) return (int)B200_OK;      // size query
+        uint8_t* p = (uint8_t*)buf;
+        memset(p, 0, need);
+        memcpy(p, KEY_CACHE_MAGIC, 8);
+        const uint64_t hdr[6] = {k->full ? 1ull : 0ull, k->domain_size, k->nA, k->nB, nH, k->nL};
+        memcpy(p + 8, hdr, sizeof hdr);
+        size_t off = 8 + sizeof hdr;
+        auto d2h = [&](const void* d, size_t bytes) { if (bytes) B200_CUDA_CHECK(cudaMemcpy(p + off, d, bytes, cudaMemcpyDeviceToHost)); };
+        d2h(k->consts_g1, 192); off += 192;
+        d2h(k->consts_g2, 256); off += 256;
+        d2h(k->A_idx, k->nA * 4); off += pad8(k->nA * 4);
+        d2h(k->B_idx, k->nB * 4); off += pad8(k->nB * 4);
+        d2h(k->A, k->nA * 64); off += k->nA * 64;
+        d2h(k->B2, k->nB * 128); off += k->nB * 128;
+        if (k->full) { d2h(k->B1, k->nB * 64); off += k->nB * 64; }
+        if (nH) memcpy(p + off, k->H_host.data(), nH * 64);
+        off += nH * 64;
+        d2h(k->L, k->nL * 64);
+        return (int)B200_OK;
+    });
+}
+
 int b200_key_load(b200_ctx* ctx, const void* bytes, size_t len, int fmt, b200_key** out) {
     return b200_key_load_sharded(ctx, bytes, len, fmt, 0, 1, out);
 }

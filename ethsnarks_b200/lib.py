@@ -16,7 +16,7 @@ u64p = C.POINTER(C.c_uint64)
 u32p = C.POINTER(C.c_uint32)
 u8p = C.POINTER(C.c_uint8)
 
-FMT_MCL_NOZK, FMT_MCL_FULL, FMT_ALT_NOZK, FMT_ALT_FULL = 0, 1, 2, 3
+FMT_MCL_NOZK, FMT_MCL_FULL, FMT_ALT_NOZK, FMT_ALT_FULL, FMT_CACHE = 0, 1, 2, 3, 4
 OP_MUL, OP_ADD, OP_SUB, OP_TO_MONT, OP_FROM_MONT, OP_INV, OP_SQR, OP_NEG, OP_INV_BINARY = range(9)
 NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT = range(4)
 
@@ -27,7 +27,7 @@ SYMBOLS = [
     "b200_g2_fixed_base", "b200_ntt", "b200_msm_g1", "b200_msm_g2", "b200_bases_upload", "b200_bases_generate",
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
-    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach",
+    "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
 ]
 
 
@@ -260,8 +260,11 @@ class ProvingKey:
     @staticmethod
     def load(ctx, pk_bytes, fmt=FMT_MCL_NOZK, rank=0, world=1):
         h = C.c_void_p()
-        buf = (C.c_char * len(pk_bytes)).from_buffer_copy(pk_bytes)
-        ctx.check(ctx.lib.b200_key_load_sharded(ctx.h, buf, C.c_size_t(len(pk_bytes)), fmt, rank, world, C.byref(h)), "key_load")
+        if isinstance(pk_bytes, np.ndarray):
+            buf, n = pk_bytes.ctypes.data_as(C.c_void_p), pk_bytes.nbytes
+        else:
+            buf, n = C.cast(C.c_char_p(bytes(pk_bytes) if not isinstance(pk_bytes, bytes) else pk_bytes), C.c_void_p), len(pk_bytes)
+        ctx.check(ctx.lib.b200_key_load_sharded(ctx.h, buf, C.c_size_t(n), fmt, rank, world, C.byref(h)), "key_load")
         return ProvingKey(ctx, h)
 
     @staticmethod
@@ -275,6 +278,14 @@ class ProvingKey:
             bi.ctypes.data_as(u32p) if bi is not None else None, H.h, L.h, _p64(g1c), _p64(g2c), C.c_uint64(num_variables),
             C.c_uint64(num_inputs), C.byref(h)), "key_from_bases")
         return ProvingKey(ctx, h, keep=(A, B_g2, B_g1, H, L))
+
+    def export_cache(self):
+        """The key as a device-native cache blob (FMT_CACHE); reload it with ProvingKey.load(ctx, blob, FMT_CACHE)."""
+        n = C.c_size_t(0)
+        self.ctx.check(self.ctx.lib.b200_key_export(self.h, None, C.c_size_t(0), C.byref(n)), "key_export")
+        buf = np.zeros(n.value, np.uint8)
+        self.ctx.check(self.ctx.lib.b200_key_export(self.h, buf.ctypes.data_as(C.c_void_p), n, C.byref(n)), "key_export")
+        return buf
 
     def attach(self, ctx):
         """A second prove slot on this resident key, bound to another Context on the same device (pipelined proving)."""

@@ -39,7 +39,8 @@ typedef struct b200_bases b200_bases;
 enum { B200_OK = 0, B200_ERR_CUDA = 1, B200_ERR_ARG = 2, B200_ERR_FORMAT = 3, B200_ERR_STATE = 4 };
 /* proving-key byte layouts: mcl points (default CURVE=MCL_BN128 build) or libff alt_bn128 points; "NOZK" =
  * r1cs_gg_ppzksnark_zok_proving_key_nozk (B query in G2 only), "FULL" = …_proving_key (B query = G2,G1 pairs). */
-enum { B200_FMT_MCL_NOZK = 0, B200_FMT_MCL_FULL = 1, B200_FMT_ALT_NOZK = 2, B200_FMT_ALT_FULL = 3 };
+enum { B200_FMT_MCL_NOZK = 0, B200_FMT_MCL_FULL = 1, B200_FMT_ALT_NOZK = 2, B200_FMT_ALT_FULL = 3,
+       B200_FMT_CACHE = 4 /* device-native key cache written by b200_key_export */ };
 enum { B200_OP_MUL = 0, B200_OP_ADD = 1, B200_OP_SUB = 2, B200_OP_TO_MONT = 3, B200_OP_FROM_MONT = 4, B200_OP_INV = 5, B200_OP_SQR = 6, B200_OP_NEG = 7, B200_OP_INV_BINARY = 8 };
 enum { B200_NTT_FFT = 0, B200_NTT_IFFT = 1, B200_NTT_COSET_FFT = 2, B200_NTT_ICOSET_FFT = 3 };
 
@@ -108,6 +109,10 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
 /* multi-GPU with b200_key_from_bases: declare that A / B_g2 / L hold this rank's slice (L starting at entry L_lo of the
  * full L query) and that H is the full query, to be sliced by rank at b200_circuit_load.  Call before circuit_load. */
 int b200_key_set_shard(b200_key* key, int rank, int world, uint64_t L_lo);
+/* Device-native key cache: writes the key's arrays as they sit in HBM (B200_FMT_CACHE) so that a reload is a few large
+ * copies instead of the point-by-point parse of the reference layout (...zok.tcc:124-143, sparse_vector.tcc:292-322).
+ * Call with buf = NULL to get the size in *len.  Only for a whole key loaded from bytes, before b200_circuit_load. */
+int b200_key_export(b200_key* key, void* buf, size_t cap, size_t* len);
 /* A second prove slot on a resident key for pipelined proving (the reference's ProverContext reuse,
  * r1cs_gg_ppzksnark_zok.hpp:279-291): shares every read-only device buffer of `key` (bases, window tables, circuit, domain)
  * and owns only its witness / evaluation buffers, bound to another context (same device), so two proofs can be in flight

@@ -423,3 +423,76 @@ def test_key_attach_second_prove_slot_and_handle_lifetimes(ctx):
     ctx3.close()
     assert not orphan.h
     orphan.free()
+
+
+def test_prove_full_size_2p20_identical_to_oracle(ctx):
+    """BASELINE.json configs[3] at its headline size: the synthetic 2^20-constraint R1CS (r1cs_examples.tcc:25-93) under a
+    REAL key made by the oracle's generator, read by the GPU from the reference's pk byte layout: witness map, H and the
+    proof are bit-identical to the oracle's; the proof also passes the in-the-exponent check."""
+    import time
+    log_m = 20
+    circ = orc.Circuit.synth_field((1 << log_m) - 2, 1)
+    assert circ.m == 1 << log_m
+    w = circ.witness()
+    key = orc.Key(circ)
+    pk_bytes = key.serialize(orc.FMT_MCL_NOZK)
+    t0 = time.time()
+    pk = eb.ProvingKey.load(ctx, pk_bytes, eb.FMT_MCL_NOZK)
+    pk.load_circuit(circ.matrix(0), circ.matrix(1), circ.matrix(2), circ.coeffs(), circ.ni, circ.nv)
+    print("key ingest (reference mcl layout) + circuit load + window tables: %.2f s for %d MB" % (time.time() - t0, len(pk_bytes) >> 20))
+    t0 = time.time()
+    raw = eb.ProvingKey.load(ctx, pk_bytes, eb.FMT_MCL_NOZK)
+    t_parse = time.time() - t0
+    blob = raw.export_cache()
+    raw.free()
+    t0 = time.time()
+    cached = eb.ProvingKey.load(ctx, blob, eb.FMT_CACHE)
+    t_cache = time.time() - t0
+    cached.free()
+    print("key ingest alone: reference layout %.2f s (%.0f MB/s), device-native cache %.2f s (%.0f MB/s)"
+          % (t_parse, len(pk_bytes) / t_parse / 1e6, t_cache, blob.nbytes / t_cache / 1e6))
+    del pk_bytes, blob
+    want = key.prove(w)
+    got = pk.prove(w)
+    for g, e in zip(got, want):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    assert key.check_in_exponent(w, got) == 0
+    assert np.array_equal(pk.h_poly(w), circ.h_poly(w)[:circ.m])
+    pk.free()
+
+
+def test_key_cache_round_trip(ctx):
+    """b200_key_export / B200_FMT_CACHE: a key parsed from the reference layout, exported as the
+    device-native cache and reloaded (whole, and sharded 1/2) proves to the same points; corrupt caches are rejected."""
+    circ = orc.Circuit.synth_field(5000, 2, 7, 8)
+    w = circ.witness()
+    key = orc.Key(circ)
+    want = key.prove(w)
+    for fo, fg in ((orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK), (orc.FMT_ALT_FULL, eb.FMT_ALT_FULL)):
+        src = eb.ProvingKey.load(ctx, key.serialize(fo), fg)
+        blob = src.export_cache()
+        src.free()
+        pk = eb.ProvingKey.load(ctx, blob, eb.FMT_CACHE)
+        pk.load_circuit(circ.matrix(0), circ.matrix(1), circ.matrix(2), circ.coeffs(), circ.ni, circ.nv)
+        got = pk.prove(w)
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+        with pytest.raises(eb.B200Error):
+            pk.export_cache()                     # only before circuit_load
+        pk.free()
+        parts, flags, keys = [], [], []
+        for r in range(2):
+            pr = eb.ProvingKey.load(ctx, blob, eb.FMT_CACHE, rank=r, world=2)
+            pr.load_circuit(circ.matrix(0), circ.matrix(1), circ.matrix(2), circ.coeffs(), circ.ni, circ.nv)
+            p, f = pr.prove_partial(w)
+            parts.append(p); flags.append(f); keys.append(pr)
+        got = keys[0].combine(np.stack(parts), np.stack(flags))
+        for pr in keys:
+            pr.free()
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+        bad = blob.copy(); bad[0] ^= 1
+        with pytest.raises(eb.B200Error):
+            eb.ProvingKey.load(ctx, bad, eb.FMT_CACHE)
+        with pytest.raises(eb.B200Error):
+            eb.ProvingKey.load(ctx, blob[:len(blob) // 2].copy(), eb.FMT_CACHE)
