@@ -37,6 +37,7 @@ struct b200_ctx {
     cudaEvent_t ev_witness = nullptr;
     int lane = 0;                      // lane the next kernels / scratch requests go to
     int overlap = 1;
+    bool fixed_table_ready[2] = {false, false};   // generator window tables of the fixed-base kernel (G1, G2) built
     cudaStream_t cur() const { return lane ? lanes[lane] : stream; }
 
     void* scratch(const char* name, size_t bytes);   // throws std::runtime_error on failure
@@ -134,5 +135,13 @@ void csr_free(DeviceCsr* c);
 // out[row] = sum coeffs[cidx[k]] * w[col[k]]  for row < n_rows
 void spmv(b200_ctx* ctx, const DeviceCsr& M, const void* d_coeffs, const void* d_w, void* d_out);
 void witness_rows(b200_ctx* ctx, const void* d_w, void* d_a, void* d_b, void* d_c, uint64_t nc, uint64_t ni, uint64_t m);
+
+// --- key generator scalars (gen.cu) -----------------------------------------------------------------------------
+void gen_consts(b200_ctx* ctx, const void* d_toxic, uint32_t logm, void* d_consts);
+void gen_lagrange(b200_ctx* ctx, const void* d_toxic, const void* d_consts, const Domain& dom, void* d_u);
+void gen_add_inputs(b200_ctx* ctx, void* d_At, const void* d_u, uint64_t nc, uint64_t ni);
+void gen_abc(b200_ctx* ctx, const void* d_toxic, const void* d_consts, const void* At, const void* Bt, const void* Ct, uint64_t ni, uint64_t nv,
+             void* d_out);
+void gen_h(b200_ctx* ctx, const void* d_toxic, const void* d_consts, uint64_t n, void* d_out);
 
 }  // namespace b200

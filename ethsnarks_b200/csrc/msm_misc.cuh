@@ -49,29 +49,56 @@ static void g_finish_t(b200_ctx* ctx, const void* xt, int nx, const void* at, in
     B200_CUDA_CHECK(cudaGetLastError());
 }
 
-// out[i] = k_i * generator (affine, (0,0) for infinity); replaces batch_exp (multiexp.tcc:838-905) for synthetic keys
+// out[i] = k_i * generator (affine, (0,0) for infinity); replaces batch_exp (multiexp.tcc:838-905, the windowed fixed-base
+// exponentiation the reference's generator uses) for synthetic keys and for the key generator.
+// Table: T[w][d] = d * 2^(8 w) * generator, w < 32, d < 256 (affine; 512 KB for G1, 1 MB for G2: L2 resident), built once per
+// context; a scalar is then at most 32 mixed additions and one inversion.
 template <typename G>
-__global__ void __launch_bounds__(128) g_fixed_base_kernel(const Fr* __restrict__ scalars, size_t n, typename G::Aff* __restrict__ out) {
+__global__ void __launch_bounds__(128) g_fixed_table_kernel(typename G::Aff* __restrict__ table) {
+    typedef typename G::Pt Pt;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 32 * 256) return;
+    const int w = idx >> 8, d = idx & 255;
+    const typename G::Aff g = Gen<typename G::F>::get();
+    Pt r = Pt::inf();
+    for (int b = 7; b >= 0; --b) {
+        r.dbl();
+        if ((d >> b) & 1) r.add_mixed(g);
+    }
+    for (int b = 0; b < 8 * w; ++b) r.dbl();
+    table[idx] = r.to_affine();
+}
+template <typename G>
+__global__ void __launch_bounds__(128) g_fixed_base_kernel(const Fr* __restrict__ scalars, size_t n, const typename G::Aff* __restrict__ table,
+                                                           typename G::Aff* __restrict__ out) {
     typedef typename G::Pt Pt;
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Fr k = scalars[i].from_mont();
-    const typename G::Aff g = Gen<typename G::F>::get();
+    const Fr k = scalars[i].from_mont();
     Pt r = Pt::inf();
-    for (int l = 7; l >= 0; --l) {
-        const uint32_t w = k.v[l];
-        for (int b = 31; b >= 0; --b) {
-            r.dbl();
-            if ((w >> b) & 1) r.add_mixed(g);
-        }
+    for (int w = 0; w < 32; ++w) {
+        const uint32_t d = (k.v[w >> 2] >> ((w & 3) * 8)) & 255u;
+        if (d) r.add_mixed(table[w * 256 + d]);
     }
     out[i] = r.to_affine();
 }
 template <typename G>
 static void g_fixed_base_t(b200_ctx* ctx, const void* d_scalars, size_t n, void* d_out) {
     if (n == 0) return;
+    typedef typename G::Aff Aff;
+    const int gi = sizeof(Aff) == 64 ? 0 : 1;
+    const int lane = ctx->lane;
+    ctx->lane = 0;                     // one table per context, whichever lane asks first
+    Aff* table = (Aff*)ctx->scratch(gi ? "fixed_table_g2" : "fixed_table_g1", 32 * 256 * sizeof(Aff));
+    ctx->lane = lane;
+    if (!ctx->fixed_table_ready[gi]) {
+        g_fixed_table_kernel<G><<<64, 128, 0, ctx->stream>>>(table);
+        ctx->launches++;
+        B200_CUDA_CHECK(cudaGetLastError());
+        ctx->fixed_table_ready[gi] = true;
+    }
     unsigned grid = (unsigned)((n + 127) / 128);
-    g_fixed_base_kernel<G><<<grid, 128, 0, ctx->stream>>>((const Fr*)d_scalars, n, (typename G::Aff*)d_out);
+    g_fixed_base_kernel<G><<<grid, 128, 0, ctx->stream>>>((const Fr*)d_scalars, n, table, (Aff*)d_out);
     ctx->launches++;
     B200_CUDA_CHECK(cudaGetLastError());
 }

@@ -476,6 +476,118 @@ int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b
     });
 }
 
+// Key generator: replaces r1cs_gg_ppzksnark_zok_generator (...zok.tcc:277-449) with the toxic waste
+// supplied by the caller.  Scalars by gen.cu (Lagrange basis at t, At/Bt/Ct as transposed SpMVs, H/L/IC scalars), points by
+// the fixed-base kernel.  The queries are stored dense with identity indices; entries the reference's sparse vectors skip
+// (zero scalars) are points at infinity, which every MSM skips - the proofs are the same.  The key comes back in the
+// pre-circuit state of b200_key_load: call b200_circuit_load next (or b200_key_export to persist it).
+int b200_generate_key(b200_ctx* ctx, const b200_csr* A, const b200_csr* B, const b200_csr* C, const uint64_t* coeffs, size_t n_coeffs,
+                      uint32_t num_inputs, uint64_t num_variables, const uint64_t* toxic_mont, int full, b200_key** out, uint64_t* vk_xy) {
+    if (!ctx || !A || !B || !C || !coeffs || !n_coeffs || !toxic_mont || !out || !vk_xy) return B200_ERR_ARG;
+    if (A->n_rows != B->n_rows || A->n_rows != C->n_rows || num_inputs > num_variables) return B200_ERR_ARG;
+    *out = nullptr;
+    return Guard{ctx}.run([&] {
+        const uint64_t nc = A->n_rows, ni = num_inputs, nv = num_variables;
+        uint32_t logm = 0;
+        while (((uint64_t)1 << logm) < nc + ni + 1) ++logm;
+        if (logm < 1) logm = 1;
+        const uint64_t m = (uint64_t)1 << logm;
+        struct Tmp {   // device temporaries, freed on every exit path
+            Domain dom; DeviceCsr T[3]; std::vector<void*> bufs;
+            void* alloc(size_t bytes) { void* d = nullptr; B200_CUDA_CHECK(cudaMalloc(&d, std::max<size_t>(bytes, 16))); bufs.push_back(d); return d; }
+            ~Tmp() { for (void* d : bufs) cudaFree(d); for (int i = 0; i < 3; ++i) csr_free(&T[i]); domain_free(&dom); }
+        } tmp;
+        domain_create(ctx, logm, &tmp.dom);
+        void* d_toxic = tmp.alloc(5 * 32);
+        B200_CUDA_CHECK(cudaMemcpyAsync(d_toxic, toxic_mont, 5 * 32, cudaMemcpyHostToDevice, ctx->stream));
+        void* d_consts = tmp.alloc(5 * 32);
+        gen_consts(ctx, d_toxic, logm, d_consts);
+        uint64_t z[4];
+        B200_CUDA_CHECK(cudaMemcpyAsync(z, d_consts, 32, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        if (!(z[0] | z[1] | z[2] | z[3])) throw std::invalid_argument("generate_key: t lies in the evaluation domain");
+        void* d_u = tmp.alloc(m * 32);
+        gen_lagrange(ctx, d_toxic, d_consts, tmp.dom, d_u);
+        void* d_coeffs = tmp.alloc(n_coeffs * 32);
+        B200_CUDA_CHECK(cudaMemcpyAsync(d_coeffs, coeffs, n_coeffs * 32, cudaMemcpyHostToDevice, ctx->stream));
+        // At, Bt, Ct: row j of the transposed matrix lists (constraint, coefficient) pairs of variable j
+        const b200_csr* mats[3] = {A, B, C};
+        void* d_xt[3];
+        for (int k3 = 0; k3 < 3; ++k3) {
+            const b200_csr* M = mats[k3];
+            const uint64_t nnz = nc ? M->row_ptr[nc] : 0;
+            std::vector<uint64_t> rp(nv + 2, 0);
+            for (uint64_t j = 0; j < nnz; ++j) {
+                if (M->col[j] > nv) throw std::invalid_argument("generate_key: variable index out of range");
+                if (M->coeff_idx[j] >= n_coeffs) throw std::invalid_argument("generate_key: coefficient index out of range");
+                rp[M->col[j] + 1]++;
+            }
+            for (uint64_t j = 0; j <= nv; ++j) rp[j + 1] += rp[j];
+            std::vector<uint32_t> col(std::max<uint64_t>(nnz, 1)), ci(std::max<uint64_t>(nnz, 1));
+            std::vector<uint64_t> cur(rp.begin(), rp.end() - 1);
+            for (uint64_t r = 0; r < nc; ++r)
+                for (uint64_t j = M->row_ptr[r]; j < M->row_ptr[r + 1]; ++j) {
+                    const uint64_t pos = cur[M->col[j]]++;
+                    col[pos] = (uint32_t)r; ci[pos] = M->coeff_idx[j];
+                }
+            csr_upload(ctx, rp.data(), col.data(), ci.data(), nv + 1, &tmp.T[k3]);
+            d_xt[k3] = tmp.alloc((nv + 1) * 32);
+            spmv(ctx, tmp.T[k3], d_coeffs, d_u, d_xt[k3]);
+        }
+        gen_add_inputs(ctx, d_xt[0], d_u, nc, ni);
+        void* d_abc = tmp.alloc((nv + 1) * 32);
+        gen_abc(ctx, d_toxic, d_consts, d_xt[0], d_xt[1], d_xt[2], ni, nv, d_abc);
+        void* d_hs = tmp.alloc((m - 1) * 32);
+        gen_h(ctx, d_toxic, d_consts, m - 1, d_hs);
+
+        std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
+        k->ctx = ctx; k->full = full != 0; k->domain_size = nv + 1;
+        k->nA = k->nB = nv + 1; k->nL = nv - ni; k->L_lo = 0; k->H_total = m - 1;
+        B200_CUDA_CHECK(cudaMalloc(&k->A, (nv + 1) * 64));
+        g_fixed_base(ctx, 1, d_xt[0], nv + 1, k->A);
+        B200_CUDA_CHECK(cudaMalloc(&k->B2, (nv + 1) * 128));
+        g_fixed_base(ctx, 2, d_xt[1], nv + 1, k->B2);
+        if (k->full) {
+            B200_CUDA_CHECK(cudaMalloc(&k->B1, (nv + 1) * 64));
+            g_fixed_base(ctx, 1, d_xt[1], nv + 1, k->B1);
+        }
+        B200_CUDA_CHECK(cudaMalloc(&k->L, std::max<uint64_t>((nv - ni) * 64, 16)));
+        g_fixed_base(ctx, 1, (const char*)d_abc + (ni + 1) * 32, nv - ni, k->L);
+        void* d_ic = tmp.alloc((ni + 1) * 64);
+        g_fixed_base(ctx, 1, d_abc, ni + 1, d_ic);
+        void* d_h = tmp.alloc((m - 1) * 64);
+        g_fixed_base(ctx, 1, d_hs, m - 1, d_h);
+        // alpha_g1, beta_g1, delta_g1 | beta_g2, delta_g2, gamma_g2
+        void* d_sc = tmp.alloc(6 * 32);
+        const int g1_src[3] = {1, 2, 4}, g2_src[3] = {2, 4, 3};
+        for (int i = 0; i < 3; ++i) {
+            B200_CUDA_CHECK(cudaMemcpyAsync((char*)d_sc + i * 32, (const char*)d_toxic + g1_src[i] * 32, 32, cudaMemcpyDeviceToDevice, ctx->stream));
+            B200_CUDA_CHECK(cudaMemcpyAsync((char*)d_sc + (3 + i) * 32, (const char*)d_toxic + g2_src[i] * 32, 32, cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        B200_CUDA_CHECK(cudaMalloc(&k->consts_g1, 3 * 64));
+        g_fixed_base(ctx, 1, d_sc, 3, k->consts_g1);
+        void* d_g2c = tmp.alloc(3 * 128);
+        g_fixed_base(ctx, 2, (const char*)d_sc + 3 * 32, 3, d_g2c);
+        B200_CUDA_CHECK(cudaMalloc(&k->consts_g2, 2 * 128));
+        B200_CUDA_CHECK(cudaMemcpyAsync(k->consts_g2, d_g2c, 2 * 128, cudaMemcpyDeviceToDevice, ctx->stream));
+        std::vector<uint32_t> ident(nv + 1);
+        for (uint64_t i = 0; i <= nv; ++i) ident[i] = (uint32_t)i;
+        k->A_idx = dev_upload(ident);
+        k->B_idx = dev_upload(ident);
+        k->H_host.resize((m - 1) * 64);
+        if (m > 1) B200_CUDA_CHECK(cudaMemcpyAsync(k->H_host.data(), d_h, (m - 1) * 64, cudaMemcpyDeviceToHost, ctx->stream));
+        // verification key pieces: alpha_g1 | beta_g2 | gamma_g2 | delta_g2 | IC[0..ni]   (affine Montgomery)
+        B200_CUDA_CHECK(cudaMemcpyAsync(vk_xy, k->consts_g1, 64, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaMemcpyAsync(vk_xy + 8, d_g2c, 128, cudaMemcpyDeviceToHost, ctx->stream));                       // beta_g2
+        B200_CUDA_CHECK(cudaMemcpyAsync(vk_xy + 24, (const char*)d_g2c + 256, 128, cudaMemcpyDeviceToHost, ctx->stream));   // gamma_g2
+        B200_CUDA_CHECK(cudaMemcpyAsync(vk_xy + 40, (const char*)d_g2c + 128, 128, cudaMemcpyDeviceToHost, ctx->stream));   // delta_g2
+        B200_CUDA_CHECK(cudaMemcpyAsync(vk_xy + 56, d_ic, (ni + 1) * 64, cudaMemcpyDeviceToHost, ctx->stream));
+        B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        *out = k.release();
+        return (int)B200_OK;
+    });
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------ prove

@@ -188,6 +188,42 @@ def proof_to_json(proof, primary_input):
     return s
 
 
+def fq_from_mont(a):
+    """Montgomery Fq limbs (n x 4) -> python ints (host-side; only used for the few points of a verification key)."""
+    rinv = pow(1 << 256, -1, Q_MOD)
+    return [x * rinv % Q_MOD for x in limbs_to_ints(a)]
+
+
+def vk_to_json(vk):
+    """vk2json (src/export.cpp:124-145) over the pieces ProvingKey.generate returns."""
+    def g1(p):
+        x, y = fq_from_mont(np.asarray(p).reshape(2, 4))
+        return '"%s", "%s"' % (_hex(x), _hex(y)) if (x or y) else '"0x0", "0x1"'
+
+    def g2(p):
+        xa, xb, ya, yb = fq_from_mont(np.asarray(p).reshape(4, 4))
+        if not (xa or xb or ya or yb):
+            ya = 1
+        return '["%s", "%s"],\n ["%s", "%s"]' % (_hex(xb), _hex(xa), _hex(yb), _hex(ya))
+
+    s = "{\n"
+    s += ' "alpha" :[' + g1(vk["alpha"]) + "],\n"
+    s += ' "beta"  :[' + g2(vk["beta"]) + "],\n"
+    s += ' "gamma" :[' + g2(vk["gamma"]) + "],\n"
+    s += ' "delta" :[' + g2(vk["delta"]) + "],\n"
+    s += '"gammaABC" :[' + ",".join("[" + g1(p) + "]" for p in vk["gammaABC"]) + "]}"
+    return s
+
+
+def generate_keypair(ctx, pb, toxic, full=False):
+    """libsnark's r1cs_gg_ppzksnark_zok_generator (…zok.tcc:277-449) on the device, with the toxic waste (t, alpha, beta,
+    gamma, delta as python ints) passed in by the caller instead of drawn from FieldT::random_element().  Returns
+    (ProvingKey without a circuit, vk dict); vk_to_json(vk) is the reference's vk.json."""
+    cs = pb.get_constraint_system()
+    return _lib.ProvingKey.generate(ctx, cs.A, cs.B, cs.C, fr_to_mont(cs.coeffs), cs.num_inputs, cs.num_variables,
+                                    fr_to_mont(list(toxic)), full=full)
+
+
 def load_proving_key(ctx, pk_file_or_bytes, fmt=_lib.FMT_MCL_NOZK, rank=0, world=1):
     """ethsnarks::load_proving_key (src/stubs.cpp:36-39); a missing file raises like the reference's assert."""
     if isinstance(pk_file_or_bytes, (bytes, bytearray, memoryview)):

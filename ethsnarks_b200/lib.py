@@ -28,6 +28,7 @@ SYMBOLS = [
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
     "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
+    "b200_generate_key",
 ]
 
 
@@ -247,6 +248,17 @@ class Bases:
             pass
 
 
+def _csr_structs(mats):
+    keep, structs = [], []
+    for rp, col, ci in mats:
+        rp, col, ci = _arr(rp), _arr(col, np.uint32), _arr(ci, np.uint32)
+        if col.size == 0:
+            col = np.zeros(1, np.uint32); ci = np.zeros(1, np.uint32)
+        keep += [rp, col, ci]
+        structs.append(CSR(_p64(rp), col.ctypes.data_as(u32p), ci.ctypes.data_as(u32p), C.c_uint64(rp.size - 1)))
+    return keep, structs
+
+
 class ProvingKey:
     """Device-resident proving key (+ circuit).  Mirrors load_proving_key / ProverContext of the reference."""
 
@@ -279,6 +291,25 @@ class ProvingKey:
             C.c_uint64(num_inputs), C.byref(h)), "key_from_bases")
         return ProvingKey(ctx, h, keep=(A, B_g2, B_g1, H, L))
 
+    @staticmethod
+    def generate(ctx, A, B, Cm, coeffs_mont, num_inputs, num_variables, toxic_mont, full=False):
+        """Key generation on the device from caller-supplied toxic waste (t, alpha, beta, gamma, delta as 5 x 4 Montgomery
+        limbs).  Returns (key, vk) with vk = dict of affine Montgomery limb arrays: alpha (8), beta/gamma/delta (16),
+        gammaABC ((num_inputs + 1) x 8).  The key still needs load_circuit()."""
+        keep, structs = _csr_structs((A, B, Cm))
+        co, tox = _arr(coeffs_mont), _arr(toxic_mont).reshape(-1)
+        if tox.size != 20:
+            raise ValueError("toxic_mont must hold 5 field elements")
+        vk = np.zeros(56 + 8 * (num_inputs + 1), np.uint64)
+        h = C.c_void_p()
+        ctx.check(ctx.lib.b200_generate_key(ctx.h, C.byref(structs[0]), C.byref(structs[1]), C.byref(structs[2]), _p64(co),
+                                            C.c_size_t(co.size // 4), C.c_uint32(num_inputs), C.c_uint64(num_variables), _p64(tox),
+                                            C.c_int(1 if full else 0), C.byref(h), _p64(vk)), "generate_key")
+        del keep
+        parts = dict(alpha=vk[0:8].copy(), beta=vk[8:24].copy(), gamma=vk[24:40].copy(), delta=vk[40:56].copy(),
+                     gammaABC=vk[56:].reshape(-1, 8).copy())
+        return ProvingKey(ctx, h), parts
+
     def export_cache(self):
         """The key as a device-native cache blob (FMT_CACHE); reload it with ProvingKey.load(ctx, blob, FMT_CACHE)."""
         n = C.c_size_t(0)
@@ -308,13 +339,7 @@ class ProvingKey:
 
     def load_circuit(self, A, B, Cm, coeffs_mont, num_inputs, num_variables):
         """A, B, Cm: (row_ptr uint64, col uint32, coeff_idx uint32) triples."""
-        keep, structs = [], []
-        for rp, col, ci in (A, B, Cm):
-            rp, col, ci = _arr(rp), _arr(col, np.uint32), _arr(ci, np.uint32)
-            if col.size == 0:
-                col = np.zeros(1, np.uint32); ci = np.zeros(1, np.uint32)
-            keep += [rp, col, ci]
-            structs.append(CSR(_p64(rp), col.ctypes.data_as(u32p), ci.ctypes.data_as(u32p), C.c_uint64(rp.size - 1)))
+        keep, structs = _csr_structs((A, B, Cm))
         co = _arr(coeffs_mont)
         self.ctx.check(self.ctx.lib.b200_circuit_load(self.h, C.byref(structs[0]), C.byref(structs[1]), C.byref(structs[2]), _p64(co),
                                                       C.c_size_t(co.size // 4), C.c_uint32(num_inputs), C.c_uint64(num_variables)),

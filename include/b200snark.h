@@ -113,6 +113,14 @@ int b200_key_set_shard(b200_key* key, int rank, int world, uint64_t L_lo);
  * copies instead of the point-by-point parse of the reference layout (...zok.tcc:124-143, sparse_vector.tcc:292-322).
  * Call with buf = NULL to get the size in *len.  Only for a whole key loaded from bytes, before b200_circuit_load. */
 int b200_key_export(b200_key* key, void* buf, size_t cap, size_t* len);
+/* Key generator on the device: r1cs_gg_ppzksnark_zok_generator (src/r1cs_gg_ppzksnark_zok/
+ * r1cs_gg_ppzksnark_zok.tcc:277-449) with the toxic waste t, alpha, beta, gamma, delta (5 x 4 limbs, Montgomery) supplied by
+ * the caller, generators G1::one / G2::one.  Returns a key in the state b200_key_load leaves it in (call
+ * b200_circuit_load next) and the verification key pieces in vk_xy: alpha_g1[8] | beta_g2[16] | gamma_g2[16] | delta_g2[16] |
+ * IC[(num_inputs + 1) x 8], affine Montgomery, (0,0) = infinity.  full != 0 also builds the B query in G1. */
+int b200_generate_key(b200_ctx* ctx, const b200_csr* A, const b200_csr* B, const b200_csr* C, const uint64_t* coeff_table_mont,
+                      size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables, const uint64_t* toxic_mont, int full,
+                      b200_key** out, uint64_t* vk_xy);
 /* A second prove slot on a resident key for pipelined proving (the reference's ProverContext reuse,
  * r1cs_gg_ppzksnark_zok.hpp:279-291): shares every read-only device buffer of `key` (bases, window tables, circuit, domain)
  * and owns only its witness / evaluation buffers, bound to another context (same device), so two proofs can be in flight

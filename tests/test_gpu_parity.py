@@ -434,7 +434,19 @@ def test_prove_full_size_2p20_identical_to_oracle(ctx):
     circ = orc.Circuit.synth_field((1 << log_m) - 2, 1)
     assert circ.m == 1 << log_m
     w = circ.witness()
+    t0 = time.time()
     key = orc.Key(circ)
+    t_cpu_gen = time.time() - t0
+    # the device generator at full size, same toxic waste: same vk, and (below) the same proof
+    mats = [circ.matrix(i) for i in range(3)]
+    t0 = time.time()
+    gk, vk = eb.ProvingKey.generate(ctx, mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv, orc.sha512_rng_fr(1 << 32, 5))
+    t_gpu_gen = time.time() - t0
+    print("key generator 2^20: device %.2f s, CPU oracle port (%d threads) %.2f s" % (t_gpu_gen, os.cpu_count(), t_cpu_gen))
+    assert eb.host.vk_to_json(vk) == key.vk_json()
+    gk.load_circuit(mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv)
+    got_gen = gk.prove(w)
+    gk.free()
     pk_bytes = key.serialize(orc.FMT_MCL_NOZK)
     t0 = time.time()
     pk = eb.ProvingKey.load(ctx, pk_bytes, eb.FMT_MCL_NOZK)
@@ -454,8 +466,9 @@ def test_prove_full_size_2p20_identical_to_oracle(ctx):
     del pk_bytes, blob
     want = key.prove(w)
     got = pk.prove(w)
-    for g, e in zip(got, want):
+    for g, g2, e in zip(got, got_gen, want):
         assert np.array_equal(np.asarray(g), np.asarray(e))
+        assert np.array_equal(np.asarray(g2), np.asarray(e))
     assert key.check_in_exponent(w, got) == 0
     assert np.array_equal(pk.h_poly(w), circ.h_poly(w)[:circ.m])
     pk.free()
@@ -496,3 +509,47 @@ def test_key_cache_round_trip(ctx):
             eb.ProvingKey.load(ctx, bad, eb.FMT_CACHE)
         with pytest.raises(eb.B200Error):
             eb.ProvingKey.load(ctx, blob[:len(blob) // 2].copy(), eb.FMT_CACHE)
+
+
+@pytest.mark.parametrize("shape", [("field", 30, 3), ("field", 1000, 1), ("binary", 5000, 10), ("field", 4093, 2)])
+def test_generator_on_device_matches_oracle_generator(ctx, shape):
+    """b200_generate_key: with the oracle's toxic waste (sha512_rng(seed_base + 0..4) = t, alpha, beta,
+    gamma, delta; oracle.cpp genkey, after …zok.tcc:277-449) the device-built key gives the same vk.json and the same proof
+    points, in witness-only and in r,s mode; the proof passes the pairing verifier against the device-built vk."""
+    import pairing
+    kind, nc, ni = shape
+    circ = orc.Circuit.synth_field(nc, ni, 3, 4) if kind == "field" else orc.Circuit.synth_binary(nc, ni)
+    w = circ.witness()
+    seed_base = 1 << 32
+    key = orc.Key(circ, seed_base)
+    toxic = orc.sha512_rng_fr(seed_base, 5)
+    mats = [circ.matrix(i) for i in range(3)]
+    pk, vk = eb.ProvingKey.generate(ctx, mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv, toxic, full=True)
+    assert eb.host.vk_to_json(vk) == key.vk_json()
+    info = pk.info()
+    assert info["domain_size"] == circ.nv + 1 and info["nL"] == circ.nv - circ.ni and info["full"] == 1
+    blob = pk.export_cache()                                   # generator -> cache -> reload also works
+    pk.load_circuit(mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv)
+    r, s = orc.rand_fr_mont(2, 99)
+    for rr, ss in ((None, None), (r, s)):
+        got, want = pk.prove(w, rr, ss), key.prove(w, rr, ss)
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+    pj = json.loads(eb.proof_to_json(pk.prove(w), eb.host.fr_from_mont(w[1:1 + circ.ni])))
+    assert pairing.groth16_verify(json.loads(eb.host.vk_to_json(vk)), pj)
+    pk.free()
+    pk2 = eb.ProvingKey.load(ctx, blob, eb.FMT_CACHE)
+    pk2.load_circuit(mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv)
+    for g, e in zip(pk2.prove(w), key.prove(w)):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    pk2.free()
+
+
+def test_generator_rejects_toxic_point_in_domain(ctx):
+    circ = orc.Circuit.synth_field(30, 3)
+    toxic = orc.sha512_rng_fr(7, 5)
+    mats = [circ.matrix(i) for i in range(3)]
+    one = eb.host.fr_to_mont([1])[0]
+    toxic[0] = one                                             # t = 1 = omega^0 lies in the domain: Z(t) = 0
+    with pytest.raises(eb.B200Error):
+        eb.ProvingKey.generate(ctx, mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv, toxic)
