@@ -257,6 +257,9 @@ def run_ours(args):
     imad_peak = ctx.imad_peak(5)
     if args.window:
         ctx.set_option("window", args.window)
+    for kv in args.opt:
+        name, _, val = kv.partition("=")
+        ctx.set_option(name, int(val))
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
 
     def barrier():
@@ -485,6 +488,7 @@ def main():
     ap.add_argument("--cpu-sample-log-m", type=int, default=17)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--window", type=int, default=0, help="window size c of the key's fixed-base tables (0 = cost model)")
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value (b200_set_option), repeatable")
     ap.add_argument("--in-flight", type=int, default=1, help="prove slots per GPU driven concurrently (1 = one proof at a time)")
     ap.add_argument("--verify", type=int, default=1, help="check one proof against its closed form in the exponent (untimed)")
     args = ap.parse_args()

@@ -217,6 +217,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "precompute")) ctx->precompute = (int)value;
     else if (!strcmp(name, "overlap")) ctx->overlap = (int)value;
     else if (!strcmp(name, "reduce_1d")) ctx->reduce_1d = (int)value;
+    else if (!strcmp(name, "g2_pair")) ctx->g2_pair = (int)value;
     else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;
@@ -242,8 +243,8 @@ int b200_imad_peak(b200_ctx* ctx, int reps, double* macs_per_s) {
 
 // ------------------------------------------------------------------------------------------------ sub-operations
 int b200_field_op(b200_ctx* ctx, int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
-    if (!ctx || !a || !out || field < 0 || field > 1 || op < 0 || op > 8) return B200_ERR_ARG;
-    if ((op <= 2) && !b) return B200_ERR_ARG;
+    if (!ctx || !a || !out || field < 0 || field > 1 || op < 0 || op > 9) return B200_ERR_ARG;
+    if ((op <= 2 || op == 9) && !b) return B200_ERR_ARG;
     return Guard{ctx}.run([&] {
         DevBuf da(n * 32), db(n * 32), dout(n * 32);
         B200_CUDA_CHECK(cudaMemcpyAsync(da.p, a, n * 32, cudaMemcpyHostToDevice, ctx->stream));

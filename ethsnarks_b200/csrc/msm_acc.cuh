@@ -1,6 +1,7 @@
 #pragma once
 // The hot kernel of the MSM (stage 4 of msm_common.cuh's list) and its launcher.
 #include "msm_common.cuh"
+#include "msm_acc_pair.cuh"
 
 namespace b200 {
 
@@ -41,6 +42,14 @@ template <typename G>
 void launch_accumulate(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* skeys, const uint32_t* svals,
                        const uint64_t* offsets, const void* d_bases, void* buckets, void* pfirst, void* plast) {
     typedef typename G::Pt Pt;
+    if constexpr (sizeof(Pt) > 128) {
+        if (ctx->g2_pair) {     // one point per lane pair (msm_acc_pair.cuh)
+            msm_accumulate_g2_pair<G><<<(unsigned)((2 * p.nchunks + 127) / 128), 128, 0, st>>>(
+                skeys, svals, offsets, p.nb, p.L, (const G2Affine*)d_bases, (G2XYZZ*)buckets, (G2XYZZ*)pfirst, (G2XYZZ*)plast);
+            ctx->launches++;
+            return;
+        }
+    }
     size_t smem = 0;
     if (sizeof(Pt) > 128 && ctx->g2_acc_smem > 0) {
         smem = (size_t)ctx->g2_acc_smem;

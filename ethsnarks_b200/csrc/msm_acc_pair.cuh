@@ -1,0 +1,134 @@
+#pragma once
+// G2 accumulate with one Fq2 point spread over a PAIR of adjacent lanes: the even lane holds the c0 ("a") component of
+// X, Y, ZZ, ZZZ, the odd lane the c1 ("b") component.  Same chunk schedule and same outputs as msm_accumulate<G2T>
+// (msm_acc.cuh); the difference is the register footprint: the one-thread kernel needs 254 registers (two resident
+// blocks per SM, IMAD pipe 64 % busy, ncu r1), a lane of the pair holds half the state.
+//   x * y   in Fq2 = (xa ya - xb yb) + (xa yb + xb ya) u: each lane computes ITS component as one fused two-product
+//           Montgomery row (Fq::dot2, 200 multiply-adds) - 400 per Fq2 product against 408 for one-thread Karatsuba;
+//   x^2     = (xa + xb)(xa - xb) + (2 xa xb) u: one plain product per lane.
+// The partner's component of each operand comes through __shfl_xor_sync(.., 1) (11 exchanges of 8 limbs per mixed add,
+// ~3 % of the executed instructions).  Control flow is uniform within a pair (both lanes walk the same chunk and all the
+// special-case predicates are combined over the pair), so the pair mask is always converged.
+// Measured on the 2^20 B query (B200): 8.24 ms -> 7.54 ms, IMAD pipe 64 % -> 71 % busy (profiles/r1_ncu_g2_pair.txt).
+#include "msm_common.cuh"
+
+namespace b200 {
+
+struct HalfXYZZ { Fq X, Y, ZZ, ZZZ; };   // one Fq2 component of a G2 XYZZ point
+
+struct PairLane {
+    bool imag;        // this lane holds the b (u) component
+    uint32_t mask;    // the two lanes of the pair
+    B200_DEV Fq other(const Fq& x) const {
+        Fq r;
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) r.v[i] = __shfl_xor_sync(mask, x.v[i], 1);
+        return r;
+    }
+    B200_DEV bool both(bool f) const { const int o = __shfl_xor_sync(mask, (int)f, 1); return f && o; }   // no short circuit: both lanes shuffle
+    static B200_DEV Fq sel(bool c, const Fq& t, const Fq& f) {
+        Fq r;
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) r.v[i] = c ? t.v[i] : f.v[i];
+        return r;
+    }
+    // my component of x * y  (xm, ym mine; xo, yo the partner's)
+    B200_DEV Fq mul(const Fq& xm, const Fq& xo, const Fq& ym, const Fq& yo) const {
+        const Fq p = sel(imag, xo, xm);             // real: xa ya + (-xb) yb      imag: xa yb + xb ya
+        const Fq q = sel(imag, xm, xo.neg());
+        return Fq::dot2(p, ym, q, yo);
+    }
+    // my component of x^2
+    B200_DEV Fq sqr(const Fq& xm, const Fq& xo) const {
+        const Fq s = sel(imag, xm, xm + xo);
+        const Fq t = sel(imag, xo.dbl(), xm - xo);
+        return s * t;
+    }
+    B200_DEV Fq one() const { return imag ? Fq::zero() : Fq::one(); }
+    B200_DEV HalfXYZZ inf() const { return HalfXYZZ{Fq::zero(), one(), Fq::zero(), Fq::zero()}; }
+};
+
+// 2 * (affine p), p not at infinity (mdbl-2008-s-1); rare: only when a bucket meets the same point twice
+static __device__ __noinline__ HalfXYZZ pair_dbl_affine(PairLane ln, Fq px, Fq pxo, Fq py, Fq pyo) {
+    const Fq U = py.dbl(), Uo = pyo.dbl();
+    if (U.is_zero() && Uo.is_zero()) return ln.inf();
+    const Fq V = ln.sqr(U, Uo), Vo = ln.other(V);
+    const Fq W = ln.mul(U, Uo, V, Vo), Wo = ln.other(W);
+    const Fq S = ln.mul(px, pxo, V, Vo);
+    const Fq xx = ln.sqr(px, pxo);
+    const Fq M = xx.dbl() + xx, Mo = ln.other(M);
+    HalfXYZZ r;
+    r.X = ln.sqr(M, Mo) - S.dbl();
+    const Fq D = S - r.X, Do = ln.other(D);
+    r.Y = ln.mul(M, Mo, D, Do) - ln.mul(W, Wo, py, pyo);
+    r.ZZ = V; r.ZZZ = W;
+    return r;
+}
+
+// a += affine p   (madd-2008-s: 8M + 2S in Fq2), complete.  Every branch condition is the same in both lanes of the pair.
+// (A warp-converged formulation - full-mask shuffles, every special case resolved by selects after the generic sum - was
+// measured slower: 8.2 ms against 7.5 ms for the 2^20 B query; the partial-mask shuffles are not what limits this kernel.)
+static B200_DEV void pair_add_mixed(const PairLane& ln, HalfXYZZ& a, const Fq& px, const Fq& pxo, const Fq& py, const Fq& pyo) {
+    if (px.is_zero() && py.is_zero() && pxo.is_zero() && pyo.is_zero()) return;   // p at infinity
+    const Fq zzo = ln.other(a.ZZ);
+    if (a.ZZ.is_zero() && zzo.is_zero()) { a.X = px; a.Y = py; a.ZZ = ln.one(); a.ZZZ = ln.one(); return; }
+    const Fq zzzo = ln.other(a.ZZZ);
+    const Fq Pp = ln.mul(px, pxo, a.ZZ, zzo) - a.X, R = ln.mul(py, pyo, a.ZZZ, zzzo) - a.Y;
+    const Fq Ppo = ln.other(Pp), Ro = ln.other(R);
+    if (Pp.is_zero() && Ppo.is_zero()) {
+        if (R.is_zero() && Ro.is_zero()) a = pair_dbl_affine(ln, px, pxo, py, pyo); else a = ln.inf();
+        return;
+    }
+    const Fq PP = ln.sqr(Pp, Ppo), PPo = ln.other(PP);
+    const Fq PPP = ln.mul(Pp, Ppo, PP, PPo), PPPo = ln.other(PPP);
+    const Fq Q = ln.mul(a.X, ln.other(a.X), PP, PPo);
+    const Fq X3 = ln.sqr(R, Ro) - PPP - Q.dbl();
+    const Fq D = Q - X3;
+    a.Y = ln.mul(R, Ro, D, ln.other(D)) - ln.mul(a.Y, ln.other(a.Y), PPP, PPPo);
+    a.X = X3;
+    a.ZZ = ln.mul(a.ZZ, zzo, PP, PPo);
+    a.ZZZ = ln.mul(a.ZZZ, zzzo, PPP, PPPo);
+}
+
+static B200_DEV void pair_store(G2XYZZ* dst, bool imag, const HalfXYZZ& a) {
+    Fq* f = (Fq*)dst + (imag ? 1 : 0);      // X.a X.b Y.a Y.b ZZ.a ZZ.b ZZZ.a ZZZ.b
+    f[0] = a.X; f[2] = a.Y; f[4] = a.ZZ; f[6] = a.ZZZ;
+}
+
+#ifndef B200_G2_PAIR_MINB
+#define B200_G2_PAIR_MINB 3     // 168 registers, no spills (4 -> 128 registers with spills: 7.8 ms against 7.5 ms)
+#endif
+template <typename G>   // G2T only; a template so that only the G2 translation unit emits it
+__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_accumulate_g2_pair(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                                                             const uint64_t* __restrict__ offsets, uint32_t nb, uint32_t L,
+                                                                             const G2Affine* __restrict__ bases, G2XYZZ* __restrict__ buckets,
+                                                                             G2XYZZ* __restrict__ pfirst, G2XYZZ* __restrict__ plast) {
+    const uint64_t M = offsets[nb];
+    const uint64_t gt = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t t = gt >> 1;
+    const uint64_t start = t * L;
+    if (start >= M) return;
+    PairLane ln;
+    ln.imag = gt & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    const uint64_t end = min(start + (uint64_t)L, M);
+    uint32_t cur = keys[start];
+    bool first_run = true;
+    HalfXYZZ acc = ln.inf();
+    for (uint64_t i = start; i < end; ++i) {
+        const uint32_t k = keys[i];
+        if (k != cur) {
+            pair_store(first_run ? &pfirst[t] : &buckets[cur], ln.imag, acc);
+            first_run = false;
+            acc = ln.inf();
+            cur = k;
+        }
+        const uint32_t v = vals ? vals[i] : (uint32_t)i;
+        const Fq* b = (const Fq*)&bases[v & 0x7fffffffu];       // x.a x.b y.a y.b: a pair reads one 128-byte line
+        Fq px = b[ln.imag ? 1 : 0], py = b[ln.imag ? 3 : 2];
+        if (v >> 31) py = py.neg();
+        const Fq pxo = ln.other(px), pyo = ln.other(py);
+        pair_add_mixed(ln, acc, px, pxo, py, pyo);
+    }
+    pair_store(first_run ? &pfirst[t] : &plast[t], ln.imag, acc);
+}
+
+}  // namespace b200

@@ -277,6 +277,7 @@ __global__ void field_op_kernel(int op, const F* __restrict__ a, const F* __rest
         case 5: r = x.inv(); break;
         case 6: r = x.sqr(); break;
         case 8: r = x.inv_binary(); break;
+        case 9: r = F::dot2(x, b[i], b[i], b[i]); break;   // a b + b^2 under one reduction
         default: r = x.neg(); break;
     }
     out[i] = r;

@@ -41,7 +41,8 @@ enum { B200_OK = 0, B200_ERR_CUDA = 1, B200_ERR_ARG = 2, B200_ERR_FORMAT = 3, B2
  * r1cs_gg_ppzksnark_zok_proving_key_nozk (B query in G2 only), "FULL" = …_proving_key (B query = G2,G1 pairs). */
 enum { B200_FMT_MCL_NOZK = 0, B200_FMT_MCL_FULL = 1, B200_FMT_ALT_NOZK = 2, B200_FMT_ALT_FULL = 3,
        B200_FMT_CACHE = 4 /* device-native key cache written by b200_key_export */ };
-enum { B200_OP_MUL = 0, B200_OP_ADD = 1, B200_OP_SUB = 2, B200_OP_TO_MONT = 3, B200_OP_FROM_MONT = 4, B200_OP_INV = 5, B200_OP_SQR = 6, B200_OP_NEG = 7, B200_OP_INV_BINARY = 8 };
+enum { B200_OP_MUL = 0, B200_OP_ADD = 1, B200_OP_SUB = 2, B200_OP_TO_MONT = 3, B200_OP_FROM_MONT = 4, B200_OP_INV = 5, B200_OP_SQR = 6, B200_OP_NEG = 7, B200_OP_INV_BINARY = 8,
+       B200_OP_DOT2 = 9 /* a*b + b*b with one Montgomery reduction (the fused row product of the paired G2 kernel) */ };
 enum { B200_NTT_FFT = 0, B200_NTT_IFFT = 1, B200_NTT_COSET_FFT = 2, B200_NTT_ICOSET_FFT = 3 };
 
 /* One R1CS matrix in CSR form: row i holds sum_k coeff_table[coeff_idx[k]] * w[col[k]], k in [row_ptr[i], row_ptr[i+1]).
@@ -60,7 +61,7 @@ const char* b200_strerror(int code);
 const char* b200_last_error(b200_ctx* ctx);
 void* b200_stream(b200_ctx* ctx);                        /* the cudaStream_t every kernel of this ctx is launched on */
 unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by this library on ctx since b200_init */
-int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing", "precompute", "overlap", "reduce_1d", "affine_rounds" */
+int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing", "precompute", "overlap", "reduce_1d", "affine_rounds", "g2_pair" */
 int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
 int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);
 int b200_timing_start(b200_ctx* ctx, int i, float* ms);  /* start of phase i relative to the first phase of the call */

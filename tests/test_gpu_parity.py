@@ -31,6 +31,11 @@ def test_field_ops(ctx, field, p):
     # binary extended Euclid (the inversion the batched-affine MSM rounds use) against the same oracle
     assert np.array_equal(ctx.field_op(field, L.OP_INV_BINARY, a[:2000]), getattr(orc, name + "_inv")(a[:2000]))
     assert np.array_equal(ctx.field_op(field, L.OP_INV_BINARY, a[-9:]), getattr(orc, name + "_inv")(a[-9:]))
+    # fused two-product Montgomery row (a b + b b under one reduction), incl. the largest operands (p-1, p-1)
+    top = orc.ints_to_arr([p - 1])
+    a2, b2 = np.concatenate([a, top]), np.concatenate([b, top])
+    mul, add = getattr(orc, name + "_mul"), getattr(orc, name + "_add")
+    assert np.array_equal(ctx.field_op(field, L.OP_DOT2, a2, b2), add(mul(a2, b2), mul(b2, b2)))
 
 
 def test_fixed_base_and_group_law(ctx):
@@ -200,6 +205,29 @@ def test_msm_g2_two_dimensional_reduction(ctx):
         finally:
             ctx.set_option("window", 0)
         assert ginf == winf and np.array_equal(got, want), window
+
+
+def test_msm_g2_lane_pair_kernel_special_cases(ctx):
+    """msm_accumulate_g2_pair (one G2 point per lane pair, Fq::dot2 rows) against the one-thread kernel and the oracle on the
+    inputs that reach its special cases: repeated bases with equal scalars (doubling inside a bucket), P and -P with equal
+    scalars (bucket cancels to infinity), bases at infinity, binary scalars (one giant bucket) and negative digits."""
+    n = 2500
+    bases, inf = orc.g2_fixed_base(orc.sha512_rng_fr(1 << 45, n))
+    s = _scalar_mix(n, 77, "dense")
+    bases[1::2][:400] = bases[0::2][:400]; s[1::2][:400] = s[0::2][:400]                   # doubling
+    s[801:1200:2] = orc.fr_sub(np.zeros((200, 4), np.uint64), s[800:1200:2])            # k P + (-k) P' ...
+    bases[801:1200:2] = bases[800:1200:2]                                               # ... with P' = P: cancels
+    inf[1300:1350] = 1
+    s[1500:2500] = _scalar_mix(1000, 78, "binary")
+    want, winf = orc.msm_g2(bases, inf, s)
+    for pair in (1, 0):
+        for window in (0, 9):
+            ctx.set_option("g2_pair", pair); ctx.set_option("window", window)
+            try:
+                got, ginf = ctx.msm_g2(bases, inf, s)
+            finally:
+                ctx.set_option("g2_pair", 1); ctx.set_option("window", 0)
+            assert ginf == winf and np.array_equal(got, want), (pair, window)
 
 
 def test_msm_large_in_the_exponent(ctx):

@@ -30,12 +30,16 @@ def main():
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--groups", default="1,2")
     ap.add_argument("--affine-rounds", type=int, default=0)
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value, repeatable")
     args = ap.parse_args()
     ctx = eb.Context(0)
     peak = ctx.imad_peak(5)
     if args.chunk:
         ctx.set_option("chunk", args.chunk)
     ctx.set_option("affine_rounds", args.affine_rounds)
+    for kv in args.opt:
+        name, _, val = kv.partition("=")
+        ctx.set_option(name, int(val))
     if not args.no_check:
         import orc
     for group in [int(g) for g in args.groups.split(",")]:
