@@ -35,7 +35,7 @@ BYTES_PER_G2_POINT = 160
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the accumulate kernel at 2^20 points, from the ncu --set full
 # capture summarised in profiles/r1_ncu_msm_accumulate_2p20_full.csv (window tables: 13 table points are read per scalar,
 # so the traffic is ~12x the canonical 96/160 B per point; HBM stays under 11 % busy)
-NCU_TRAFFIC_BYTES = {("G2", 20): 1.916516e9 + 0.203396e9, ("G1", 20): 1.872888e9 + 0.104280e9}
+NCU_TRAFFIC_BYTES = {("G2", 20): 1.888617e9 + 0.202356e9, ("G1", 20): 1.872888e9 + 0.104280e9}
 
 
 # ----------------------------------------------------------------------------------------------- multi-rank helpers
@@ -424,7 +424,7 @@ def run_ours(args):
             g2 = nm == "B_g2"
             mac = (MAC_PER_G2_POINT if g2 else MAC_PER_G1_POINT) * counts[nm]
             byts = (BYTES_PER_G2_POINT if g2 else BYTES_PER_G1_POINT) * counts[nm]
-            kernels[nm] = {"kernel": "msm_accumulate<%s>" % ("G2" if g2 else "G1"), "points": counts[nm], "ms": ms,
+            kernels[nm] = {"kernel": "msm_accumulate_g2_pair" if g2 else "msm_accumulate<G1>", "points": counts[nm], "ms": ms,
                            "tmac_s": mac / (ms * 1e-3) / 1e12, "frac_imad": mac / (ms * 1e-3) / imad_peak,
                            "gb_s": byts / (ms * 1e-3) / 1e9}
     peaks = {}
