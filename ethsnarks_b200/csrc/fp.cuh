@@ -186,6 +186,41 @@ struct __align__(16) Fp {
         return r;
     }
     B200_DEV Fp neg() const { return is_zero() ? *this : (zero() - *this); }
+    // ---- operand forms for products only (NOT fully reduced; never stored, never compared) -------------------------
+    // The CIOS rows of operator* and dot2 stay inside their accumulators for operands below 2p (running total
+    // < 3p(2^32 + 1) < 2^288, result < p(4p/R + 1) < 1.76p for one product, one conditional subtraction), so the
+    // operand preparation of the lane-pair G2 kernel can skip its own reductions.
+    B200_DEV Fp neg_lazy() const {          // p - x, in (0, p]
+        Fp r;
+        asm("sub.cc.u32 %0, %8, %16;\n\t"
+            "subc.cc.u32 %1, %9, %17;\n\t"
+            "subc.cc.u32 %2, %10, %18;\n\t"
+            "subc.cc.u32 %3, %11, %19;\n\t"
+            "subc.cc.u32 %4, %12, %20;\n\t"
+            "subc.cc.u32 %5, %13, %21;\n\t"
+            "subc.cc.u32 %6, %14, %22;\n\t"
+            "subc.u32 %7, %15, %23;"
+            : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+            : "r"(P::mod(0)), "r"(P::mod(1)), "r"(P::mod(2)), "r"(P::mod(3)), "r"(P::mod(4)), "r"(P::mod(5)), "r"(P::mod(6)), "r"(P::mod(7)),
+              "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]));
+        return r;
+    }
+    static B200_DEV Fp add_lazy(const Fp& a, const Fp& b) {   // a + b, in [0, 2p)
+        Fp r;
+        asm("add.cc.u32 %0, %8, %16;\n\t"
+            "addc.cc.u32 %1, %9, %17;\n\t"
+            "addc.cc.u32 %2, %10, %18;\n\t"
+            "addc.cc.u32 %3, %11, %19;\n\t"
+            "addc.cc.u32 %4, %12, %20;\n\t"
+            "addc.cc.u32 %5, %13, %21;\n\t"
+            "addc.cc.u32 %6, %14, %22;\n\t"
+            "addc.u32 %7, %15, %23;"
+            : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+            : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+              "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+        return r;
+    }
+    static B200_DEV Fp sub_lazy(const Fp& a, const Fp& b) { return add_lazy(a, b.neg_lazy()); }   // a - b + p, in (0, 2p)
     B200_DEV Fp dbl() const { return *this + *this; }
 
     // Montgomery product a*b*R^-1 mod p, fully reduced: CIOS, one row per limb of b, on two accumulators E / O holding the

@@ -28,7 +28,9 @@ struct b200_ctx {
                                        // correct but slower than XYZZ alone on B200); -1 = by run length
     int g2_acc_smem = 0;               // dynamic shared memory requested by msm_accumulate<G2> only to cap its blocks per SM,
                                        // so that G1 accumulate blocks of the other lanes are co-resident with it
-    int g2_pair = 1;                   // G2 accumulate with one point per lane pair (msm_acc_pair.cuh); 0 = one thread per point
+    int g2_pair = 2;                   // G2 accumulate with one point per lane pair (msm_acc_pair.cuh): 2 = lazy operand forms,
+                                       // 1 = strict, 3 = lazy + out-of-line products; 0 = one thread per point
+    int finalize_chunks = 1;           // 1 = stitch chunk partial sums with one thread per chunk edge (msm_finalize_chunks)
     int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one
     int precompute = 1;                // build fixed-base window tables for resident keys / base sets
     // lanes: extra streams so the independent MSMs of one prove overlap (the latency-bound reduction tail of one MSM

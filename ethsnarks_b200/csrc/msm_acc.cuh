@@ -44,8 +44,14 @@ void launch_accumulate(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const u
     typedef typename G::Pt Pt;
     if constexpr (sizeof(Pt) > 128) {
         if (ctx->g2_pair) {     // one point per lane pair (msm_acc_pair.cuh)
-            msm_accumulate_g2_pair<G><<<(unsigned)((2 * p.nchunks + 127) / 128), 128, 0, st>>>(
-                skeys, svals, offsets, p.nb, p.L, (const G2Affine*)d_bases, (G2XYZZ*)buckets, (G2XYZZ*)pfirst, (G2XYZZ*)plast);
+            const unsigned grid = (unsigned)((2 * p.nchunks + 127) / 128);
+#define B200_PAIR_LAUNCH(MODE)                                                                                              \
+    msm_accumulate_g2_pair<G, MODE><<<grid, 128, 0, st>>>(skeys, svals, offsets, p.nb, p.L, (const G2Affine*)d_bases, (G2XYZZ*)buckets, \
+                                                          (G2XYZZ*)pfirst, (G2XYZZ*)plast)
+            if (ctx->g2_pair == 1) B200_PAIR_LAUNCH(1);          // strict operand preparation, kept as cross-check
+            else if (ctx->g2_pair == 3) B200_PAIR_LAUNCH(3);     // lazy operands + out-of-line products
+            else B200_PAIR_LAUNCH(2);                            // lazy operands
+#undef B200_PAIR_LAUNCH
             ctx->launches++;
             return;
         }

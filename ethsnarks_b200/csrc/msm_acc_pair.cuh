@@ -16,7 +16,18 @@ namespace b200 {
 
 struct HalfXYZZ { Fq X, Y, ZZ, ZZZ; };   // one Fq2 component of a G2 XYZZ point
 
+// (fp.cuh: neg_lazy, add_lazy, sub_lazy; the products themselves still return fully reduced values, so everything
+// stored or compared is canonical in every mode.)
+static __device__ __noinline__ Fq pair_dot2_ool(Fq a0, Fq b0, Fq a1, Fq b1) { return Fq::dot2(a0, b0, a1, b1); }
+static __device__ __noinline__ Fq pair_mul_ool(Fq a, Fq b) { return a * b; }
+
+// MODE 1: strict operand preparation.  MODE 2 (LAZY): the operands of the products are prepared without their own
+// reductions.  MODE 3: LAZY and the products are calls to ONE out-of-line copy each (the inlined body is ~150 KB of SASS
+// and ncu shows 15 % of the stall samples waiting for instruction fetch).
+template <int MODE>
 struct PairLane {
+    static constexpr bool LAZY = MODE >= 2;
+    static constexpr bool OOL = MODE == 3;
     bool imag;        // this lane holds the b (u) component
     uint32_t mask;    // the two lanes of the pair
     B200_DEV Fq other(const Fq& x) const {
@@ -33,13 +44,15 @@ struct PairLane {
     // my component of x * y  (xm, ym mine; xo, yo the partner's)
     B200_DEV Fq mul(const Fq& xm, const Fq& xo, const Fq& ym, const Fq& yo) const {
         const Fq p = sel(imag, xo, xm);             // real: xa ya + (-xb) yb      imag: xa yb + xb ya
-        const Fq q = sel(imag, xm, xo.neg());
+        const Fq q = sel(imag, xm, LAZY ? xo.neg_lazy() : xo.neg());
+        if (OOL) return pair_dot2_ool(p, ym, q, yo);
         return Fq::dot2(p, ym, q, yo);
     }
     // my component of x^2
     B200_DEV Fq sqr(const Fq& xm, const Fq& xo) const {
-        const Fq s = sel(imag, xm, xm + xo);
-        const Fq t = sel(imag, xo.dbl(), xm - xo);
+        const Fq s = sel(imag, xm, LAZY ? Fq::add_lazy(xm, xo) : xm + xo);
+        const Fq t = sel(imag, LAZY ? Fq::add_lazy(xo, xo) : xo.dbl(), LAZY ? Fq::sub_lazy(xm, xo) : xm - xo);
+        if (OOL) return pair_mul_ool(s, t);
         return s * t;
     }
     B200_DEV Fq one() const { return imag ? Fq::zero() : Fq::one(); }
@@ -47,7 +60,8 @@ struct PairLane {
 };
 
 // 2 * (affine p), p not at infinity (mdbl-2008-s-1); rare: only when a bucket meets the same point twice
-static __device__ __noinline__ HalfXYZZ pair_dbl_affine(PairLane ln, Fq px, Fq pxo, Fq py, Fq pyo) {
+template <int MODE>
+static __device__ __noinline__ HalfXYZZ pair_dbl_affine(PairLane<MODE> ln, Fq px, Fq pxo, Fq py, Fq pyo) {
     const Fq U = py.dbl(), Uo = pyo.dbl();
     if (U.is_zero() && Uo.is_zero()) return ln.inf();
     const Fq V = ln.sqr(U, Uo), Vo = ln.other(V);
@@ -66,7 +80,8 @@ static __device__ __noinline__ HalfXYZZ pair_dbl_affine(PairLane ln, Fq px, Fq p
 // a += affine p   (madd-2008-s: 8M + 2S in Fq2), complete.  Every branch condition is the same in both lanes of the pair.
 // (A warp-converged formulation - full-mask shuffles, every special case resolved by selects after the generic sum - was
 // measured slower: 8.2 ms against 7.5 ms for the 2^20 B query; the partial-mask shuffles are not what limits this kernel.)
-static B200_DEV void pair_add_mixed(const PairLane& ln, HalfXYZZ& a, const Fq& px, const Fq& pxo, const Fq& py, const Fq& pyo) {
+template <int MODE>
+static B200_DEV void pair_add_mixed(const PairLane<MODE>& ln, HalfXYZZ& a, const Fq& px, const Fq& pxo, const Fq& py, const Fq& pyo) {
     if (px.is_zero() && py.is_zero() && pxo.is_zero() && pyo.is_zero()) return;   // p at infinity
     const Fq zzo = ln.other(a.ZZ);
     if (a.ZZ.is_zero() && zzo.is_zero()) { a.X = px; a.Y = py; a.ZZ = ln.one(); a.ZZZ = ln.one(); return; }
@@ -96,7 +111,7 @@ static B200_DEV void pair_store(G2XYZZ* dst, bool imag, const HalfXYZZ& a) {
 #ifndef B200_G2_PAIR_MINB
 #define B200_G2_PAIR_MINB 3     // 168 registers, no spills (4 -> 128 registers with spills: 7.8 ms against 7.5 ms)
 #endif
-template <typename G>   // G2T only; a template so that only the G2 translation unit emits it
+template <typename G, int MODE>   // G2T only; a template so that only the G2 translation unit emits it
 __global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_accumulate_g2_pair(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
                                                                              const uint64_t* __restrict__ offsets, uint32_t nb, uint32_t L,
                                                                              const G2Affine* __restrict__ bases, G2XYZZ* __restrict__ buckets,
@@ -106,7 +121,7 @@ __global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_accumulate_g2_pair
     const uint64_t t = gt >> 1;
     const uint64_t start = t * L;
     if (start >= M) return;
-    PairLane ln;
+    PairLane<MODE> ln;
     ln.imag = gt & 1;
     ln.mask = 3u << (threadIdx.x & 30);
     const uint64_t end = min(start + (uint64_t)L, M);

@@ -73,8 +73,8 @@ void launch_affine_rounds(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, int 
                           const void* d_bases, const uint64_t* offsets, const uint32_t** keys_out, const void** pts_out,
                           const uint64_t** off_out);
 template <typename G>
-void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint64_t* offsets, void* buckets, const void* pfirst,
-                     const void* plast, uint32_t* big, size_t big_cap);
+void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* keys, const uint64_t* offsets, void* buckets,
+                     const void* pfirst, const void* plast, uint32_t* big, size_t big_cap);
 template <typename G>
 void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void* buckets, void* seg, void* win, void* d_out);
 

@@ -168,7 +168,7 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     launch_accumulate<G>(ctx, st, p, akeys, avals, aoff, abases, buckets, pfirst, plast);
     ctx->t_end();
     ctx->t_begin("msm.finalize");
-    launch_finalize<G>(ctx, st, p, aoff, buckets, pfirst, plast, big, big_cap);
+    launch_finalize<G>(ctx, st, p, akeys, aoff, buckets, pfirst, plast, big, big_cap);
     ctx->t_end();
     ctx->t_begin("msm.reduce");
     launch_reduce<G>(ctx, st, p, buckets, seg, win, d_out);

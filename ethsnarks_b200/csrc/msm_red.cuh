@@ -30,6 +30,42 @@ __global__ void __launch_bounds__(128) msm_finalize(const uint64_t* __restrict__
     buckets[b] = acc;
 }
 
+// The same stitching with one thread per CHUNK for the additions: thread t owns the run that crosses from chunk t-1 into
+// chunk t, if chunk t is the first one that run continues into.  With runs shorter than a chunk almost every chunk edge
+// is such a crossing, so nearly all lanes of a warp execute the one addition together, where the per-bucket kernel above
+// has ~half of its lanes idle while the others add.  The memory-only cases (empty bucket, run inside one chunk) stay per
+// bucket: thread id handles bucket id and chunk id.
+template <typename G>
+__global__ void __launch_bounds__(128) msm_finalize_chunks(const uint32_t* __restrict__ keys, const uint64_t* __restrict__ offsets, uint32_t nb,
+                                                           uint32_t L, typename G::Pt* __restrict__ buckets,
+                                                           const typename G::Pt* __restrict__ pfirst, const typename G::Pt* __restrict__ plast,
+                                                           uint32_t* __restrict__ big_count, uint32_t* __restrict__ big_list) {
+    typedef typename G::Pt Pt;
+    const uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t M = offsets[nb];
+    if (id < nb) {
+        const uint64_t s = offsets[id], e = offsets[id + 1];
+        if (s == e) buckets[id] = Pt::inf();
+        else {
+            const uint64_t t0 = s / L, t1 = (e - 1) / L;
+            if (t0 == t1) {
+                if (s == t0 * L) buckets[id] = pfirst[t0];
+                else if (e == min((t0 + 1) * (uint64_t)L, M)) buckets[id] = plast[t0];
+            }
+        }
+    }
+    const uint64_t pos = id * L;
+    if (id == 0 || pos >= M) return;
+    const uint32_t b = keys[pos];
+    const uint64_t s = offsets[b];
+    if (s >= pos || s / L != id - 1) return;          // no crossing here, or an earlier chunk already owns this run
+    const uint64_t t0 = id - 1, t1 = (offsets[b + 1] - 1) / L;
+    if (t1 - t0 > B200_BIG_SPAN) { big_list[atomicAdd(big_count, 1u)] = b; return; }
+    Pt acc = (s == t0 * L) ? pfirst[t0] : plast[t0];
+    for (uint64_t t = id; t <= t1; ++t) acc.add(pfirst[t]);
+    buckets[b] = acc;
+}
+
 template <typename Pt>
 B200_DEV void block_tree_reduce(Pt& acc, Pt* sh) {   // blockDim.x == 128; result in thread 0's acc
     sh[threadIdx.x] = acc;
@@ -224,15 +260,20 @@ __global__ void msm_horner(const typename G::Pt* __restrict__ win, int W, int c,
 
 // ------------------------------------------------------------------------------------------------- launchers
 template <typename G>
-void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint64_t* offsets, void* buckets_, const void* pfirst_,
-                     const void* plast_, uint32_t* big, size_t big_cap) {
+void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* keys, const uint64_t* offsets, void* buckets_,
+                     const void* pfirst_, const void* plast_, uint32_t* big, size_t big_cap) {
     typedef typename G::Pt Pt;
     Pt* buckets = (Pt*)buckets_;
     const Pt* pfirst = (const Pt*)pfirst_;
     const Pt* plast = (const Pt*)plast_;
     const size_t smem = 128 * sizeof(Pt);     // <= 32 KB, inside the default dynamic shared memory limit
     B200_CUDA_CHECK(cudaMemsetAsync(big, 0, 4, st));
-    msm_finalize<G><<<(p.nb + 127) / 128, 128, 0, st>>>(offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+    if (ctx->finalize_chunks) {
+        const uint64_t threads = std::max<uint64_t>(p.nb, p.nchunks);
+        msm_finalize_chunks<G><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(keys, offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+    } else {
+        msm_finalize<G><<<(p.nb + 127) / 128, 128, 0, st>>>(offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+    }
     msm_finalize_big<G><<<(unsigned)std::min<size_t>(big_cap, 1024), 128, smem, st>>>(offsets, p.L, buckets, pfirst, plast, big, big + 1);
     ctx->launches += 2;
 }

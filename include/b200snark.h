@@ -61,7 +61,7 @@ const char* b200_strerror(int code);
 const char* b200_last_error(b200_ctx* ctx);
 void* b200_stream(b200_ctx* ctx);                        /* the cudaStream_t every kernel of this ctx is launched on */
 unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by this library on ctx since b200_init */
-int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing", "precompute", "overlap", "reduce_1d", "affine_rounds", "g2_pair" */
+int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing", "precompute", "overlap", "reduce_1d", "affine_rounds", "g2_pair", "finalize_chunks" */
 int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
 int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);
 int b200_timing_start(b200_ctx* ctx, int i, float* ms);  /* start of phase i relative to the first phase of the call */

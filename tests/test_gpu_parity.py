@@ -220,14 +220,43 @@ def test_msm_g2_lane_pair_kernel_special_cases(ctx):
     inf[1300:1350] = 1
     s[1500:2500] = _scalar_mix(1000, 78, "binary")
     want, winf = orc.msm_g2(bases, inf, s)
-    for pair in (1, 0):
+    for pair in (3, 2, 1, 0):     # 2: product operands prepared without their own reductions (neg_lazy / add_lazy / sub_lazy)
         for window in (0, 9):
             ctx.set_option("g2_pair", pair); ctx.set_option("window", window)
             try:
                 got, ginf = ctx.msm_g2(bases, inf, s)
             finally:
-                ctx.set_option("g2_pair", 1); ctx.set_option("window", 0)
+                ctx.set_option("g2_pair", 2); ctx.set_option("window", 0)
             assert ginf == winf and np.array_equal(got, want), (pair, window)
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_msm_finalize_per_chunk_edge(ctx, group):
+    """msm_finalize_chunks (one thread per chunk edge) against the per-bucket stitching and the oracle: short chunks so that
+    runs cross several edges, binary scalars (a bucket spanning more chunks than B200_BIG_SPAN), infinity bases, both
+    G2 accumulate kernels, with and without window tables."""
+    n = 6000
+    fix, omsm = (orc.g1_fixed_base, orc.msm_g1) if group == 1 else (orc.g2_fixed_base, orc.msm_g2)
+    xy, inf = fix(orc.sha512_rng_fr(1 << 46, n))
+    inf[11] = 1
+    s = _scalar_mix(n, 91, "dense")
+    s[3000:] = _scalar_mix(3000, 92, "binary")
+    want, winf = omsm(xy, inf, s)
+    plain, tabled = eb.Bases(ctx, group, xy=xy, inf=inf), eb.Bases(ctx, group, xy=xy, inf=inf)
+    try:
+        for window, chunk, pair in ((0, 0, 1), (5, 4, 2), (7, 16, 0), (3, 2, 3)):
+            for fc in (1, 0):
+                ctx.set_option("finalize_chunks", fc); ctx.set_option("window", window)
+                ctx.set_option("chunk", chunk); ctx.set_option("g2_pair", pair)
+                got, gi = plain.msm(s)
+                assert gi == winf and np.array_equal(got, want), (window, chunk, pair, fc, "plain")
+                tabled.precompute(window)
+                got, gi = tabled.msm(s)
+                assert gi == winf and np.array_equal(got, want), (window, chunk, pair, fc, "tables")
+    finally:
+        ctx.set_option("finalize_chunks", 1); ctx.set_option("window", 0)
+        ctx.set_option("chunk", 0); ctx.set_option("g2_pair", 2)
+        plain.free(); tabled.free()
 
 
 def test_msm_large_in_the_exponent(ctx):

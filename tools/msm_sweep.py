@@ -4,6 +4,11 @@
 Bases are k_i * G (distinct, generated on the GPU), scalars uniform < 2^253; each result is checked "in the exponent"
 against the CPU oracle: MSM == (sum k_i s_i) * G.  Prints one JSON line per (group, N).
   python tools/msm_sweep.py [--min 16] [--max 24] [--g2-max 22] [--reps 3] [--no-check]
+
+Under torchrun (one process per GPU, NCCL) the (base, scalar) index range is split evenly over the ranks: every
+rank runs the whole window pipeline on its slice, the affine partial sums (8 or 16 limbs + flag per rank) are all-gathered
+and rank 0 adds them.  Timed on the device: max over ranks of the MSM's own CUDA-event time plus the all-gather + additions.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 tools/msm_sweep.py
 """
 import argparse
 import json
@@ -16,7 +21,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import torch  # noqa: E402
 import ethsnarks_b200 as eb  # noqa: E402
-from bench import rand_scalars, MAC_PER_G1_POINT, MAC_PER_G2_POINT  # noqa: E402
+from bench import rand_scalars, shard_range, max_over_ranks, MAC_PER_G1_POINT, MAC_PER_G2_POINT  # noqa: E402
 
 
 def main():
@@ -32,7 +37,14 @@ def main():
     ap.add_argument("--affine-rounds", type=int, default=0)
     ap.add_argument("--opt", action="append", default=[], help="library option name=value, repeatable")
     args = ap.parse_args()
-    ctx = eb.Context(0)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = eb.Context(local)
     peak = ctx.imad_peak(5)
     if args.chunk:
         ctx.set_option("chunk", args.chunk)
@@ -47,32 +59,61 @@ def main():
             n = 1 << logn
             k = rand_scalars(n, 1000 + logn)
             s = rand_scalars(n, 2000 + logn)
-            bases = eb.Bases(ctx, group, scalars=k)
+            lo, hi = shard_range(n, rank, world)
+            bases = eb.Bases(ctx, group, scalars=np.ascontiguousarray(k[lo:hi]))
             if args.tables:
                 bases.precompute(0)
-            s_dev = torch.from_numpy(s.view(np.int64)).cuda()
+            s_dev = torch.from_numpy(np.ascontiguousarray(s[lo:hi]).view(np.int64)).cuda()
             torch.cuda.synchronize()
             times, sub = [], {}
+            limbs = 8 if group == 1 else 16
             for r in range(args.reps + 1):
-                got, inf = bases.msm(device_ptr=s_dev.data_ptr(), n=n)
+                if world > 1:
+                    dist.barrier()
+                got, inf = bases.msm(device_ptr=s_dev.data_ptr(), n=hi - lo)
                 t = dict(ctx.timings())
+                if world > 1:
+                    # the one exchange step: all ranks' affine partial sums, then <= world - 1 additions
+                    part = np.zeros(limbs + 1, dtype=np.uint64)
+                    part[:limbs] = np.asarray(got).reshape(-1)
+                    part[limbs] = int(np.asarray(inf).reshape(-1)[0])
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    pin = torch.from_numpy(part.view(np.int64)).pin_memory()
+                    e0.record()
+                    mine = pin.cuda(non_blocking=True)
+                    allp = [torch.empty_like(mine) for _ in range(world)]
+                    dist.all_gather(allp, mine)
+                    host = torch.stack(allp).cpu().numpy().view(np.uint64)
+                    got, inf = host[0, :limbs].copy(), np.array([host[0, limbs]], dtype=np.uint8)
+                    add = ctx.g1_add if group == 1 else ctx.g2_add
+                    for q in range(1, world):
+                        got, inf = add(got.reshape(1, limbs), inf, host[q, :limbs].reshape(1, limbs).copy(),
+                                       np.array([host[q, limbs]], dtype=np.uint8))
+                    got = np.asarray(got).reshape(-1)
+                    e1.record()
+                    torch.cuda.synchronize()
+                    t["msm.exchange"] = e0.elapsed_time(e1)
+                    t["msm.total"] = max_over_ranks(t["msm.total"]) + max_over_ranks(t["msm.exchange"])
                 if r:
                     times.append(t["msm.total"])
                     for kk, v in t.items():
                         sub.setdefault(kk, []).append(v)
             ok = None
-            if not args.no_check:
+            if not args.no_check and rank == 0:
                 want, _ = (orc.g1_fixed_base if group == 1 else orc.g2_fixed_base)(orc.fr_dot(k, s).reshape(1, 4))
-                ok = bool(np.array_equal(got, want[0]))
+                ok = bool(np.array_equal(np.asarray(got).reshape(-1), np.asarray(want[0]).reshape(-1)))
             ms = float(np.min(times))
             mac = (MAC_PER_G1_POINT if group == 1 else MAC_PER_G2_POINT) * n
-            print(json.dumps({"group": "G%d" % group, "log_n": logn, "ms": ms, "mpoints_per_s": n / ms / 1e3,
-                              "tmac_s_canonical": mac / (ms * 1e-3) / 1e12, "frac_of_imad_peak": mac / (ms * 1e-3) / peak,
+            if rank == 0:
+              print(json.dumps({"group": "G%d" % group, "log_n": logn, "n_gpus": world, "ms": ms, "mpoints_per_s": n / ms / 1e3,
+                              "tmac_s_canonical": mac / (ms * 1e-3) / 1e12, "frac_of_imad_peak": mac / (ms * 1e-3) / peak / world,
                               "imad_peak_tmac_s": peak / 1e12, "in_exponent_ok": ok, "tables": bool(args.tables), "chunk": args.chunk, "affine_rounds": args.affine_rounds,
                               "phases_ms": {kk: round(float(np.min(v)), 4) for kk, v in sub.items()}}), flush=True)
             bases.free()
             del s_dev
             torch.cuda.empty_cache()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
