@@ -218,6 +218,8 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "overlap")) ctx->overlap = (int)value;
     else if (!strcmp(name, "reduce_1d")) ctx->reduce_1d = (int)value;
     else if (!strcmp(name, "g2_pair")) ctx->g2_pair = (int)value;
+    else if (!strcmp(name, "ntt_radix4")) ctx->ntt_radix4 = (int)value;
+    else if (!strcmp(name, "reduce_fold")) ctx->reduce_fold = (int)value;
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
     else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;
     else return B200_ERR_ARG;

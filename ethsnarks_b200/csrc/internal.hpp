@@ -31,6 +31,9 @@ struct b200_ctx {
     int g2_pair = 2;                   // G2 accumulate with one point per lane pair (msm_acc_pair.cuh): 2 = lazy operand forms,
                                        // 1 = strict, 3 = lazy + out-of-line products; 0 = one thread per point
     int finalize_chunks = 1;           // 1 = stitch chunk partial sums with one thread per chunk edge (msm_finalize_chunks)
+    int ntt_radix4 = 1;                // 1 = NTT passes with two stages per shared-memory round trip (ntt_pass4)
+    int reduce_fold = 1;               // stage B of the 2D bucket reduction as halving passes (msm_rc_fold): 1 = for bucket sets of
+                                       // >= 2^17 (measured: pays from there on, costs ~20 us of extra launches below), 2 = always, 0 = never
     int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one
     int precompute = 1;                // build fixed-base window tables for resident keys / base sets
     // lanes: extra streams so the independent MSMs of one prove overlap (the latency-bound reduction tail of one MSM

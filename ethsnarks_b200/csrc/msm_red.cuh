@@ -202,6 +202,34 @@ __global__ void __launch_bounds__(32) msm_rc_sum(const typename G::Pt* __restric
     warp_tree_reduce(acc);
     if (threadIdx.x == 0) V[(size_t)blockIdx.y * (S + Rn) + o] = acc;
 }
+// Stage B as halving passes, one THREAD per addition: pass j adds the upper half of the surviving partial column sums onto
+// the lower half (pc is [group][lo], so that is pc[i] += pc[i + n/2]) and the upper half of every row's surviving partial
+// sums onto its lower half.  Every pass is one addition deep with as many threads as additions, where the warp-per-output
+// kernel above chains cnt/32 + 5 additions in a few hundred warps (G2, 2^19 buckets: 1.14 ms against 7 x ~35 us).
+// The last pass of each kind writes V.  colcur = surviving column partials per bucket set (> S), rwl = log2 of the row
+// width AFTER this pass; either side may already be finished (colcur == S / rows_active == 0).
+template <typename G>
+__global__ void __launch_bounds__(128) msm_rc_fold(typename G::Pt* __restrict__ pc, uint32_t ncol, uint32_t colcur,
+                                                   typename G::Pt* __restrict__ pr, uint32_t nrow, uint32_t rw0, uint32_t rwl, uint32_t rows_active,
+                                                   uint32_t S, uint32_t Rn, typename G::Pt* __restrict__ V) {
+    typedef typename G::Pt Pt;
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t nc2 = colcur > S ? colcur >> 1 : 0;
+    if (id < nc2) {
+        Pt* src = pc + (size_t)blockIdx.y * ncol;
+        Pt a = src[id];
+        a.add(src[id + nc2]);
+        if (nc2 == S) V[(size_t)blockIdx.y * (S + Rn) + id] = a; else src[id] = a;
+        return;
+    }
+    id -= nc2;
+    if (!rows_active || id >= (Rn << rwl)) return;
+    const uint32_t hi = id >> rwl, lg = id & ((1u << rwl) - 1);
+    Pt* src = pr + (size_t)blockIdx.y * nrow + (size_t)hi * rw0;
+    Pt a = src[lg];
+    a.add(src[lg + (1u << rwl)]);
+    if (rwl == 0) V[(size_t)blockIdx.y * (S + Rn) + S + hi] = a; else src[lg] = a;
+}
 // Stage C: one warp per (weight bit i, slice of B200_RC_SLICE entries of V): sum of the selected C_lo and R_hi.
 #define B200_RC_SLICE 128
 template <typename G>
@@ -299,7 +327,22 @@ void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void*
         const uint32_t nslice = (S + Rn + B200_RC_SLICE - 1) / B200_RC_SLICE;
         Pt* Us = (Pt*)ctx->scratch("msm_rc_us", (size_t)Wr * nbits * nslice * sizeof(Pt));
         msm_rc_partial<G><<<dim3((ncol + nrow + 127) / 128, Wr), 128, 0, st>>>(B, p.half, s, K, pc, pr);
-        msm_rc_sum<G><<<dim3(S + Rn, Wr), 32, 0, st>>>(pc, pr, p.half, s, K, V);
+        if ((ctx->reduce_fold == 2 || (ctx->reduce_fold == 1 && p.half >= (1u << 17))) && Rn / Kc >= 2 && S / Kr >= 2) {
+            uint32_t colcur = ncol, rw = S / Kr;
+            while (colcur > S || rw > 1) {
+                const uint32_t nc2 = colcur > S ? colcur / 2 : 0;
+                uint32_t rwl = 0;
+                while (rw > 1 && (2u << rwl) < rw) ++rwl;          // log2(rw / 2)
+                const uint32_t nr2 = rw > 1 ? Rn << rwl : 0;
+                msm_rc_fold<G><<<dim3((nc2 + nr2 + 127) / 128, Wr), 128, 0, st>>>(pc, ncol, colcur, pr, nrow, S / Kr, rwl, rw > 1, S, Rn, V);
+                ctx->launches++;
+                if (colcur > S) colcur /= 2;
+                if (rw > 1) rw /= 2;
+            }
+            ctx->launches--;      // the common count below assumes one stage-B launch
+        } else {
+            msm_rc_sum<G><<<dim3(S + Rn, Wr), 32, 0, st>>>(pc, pr, p.half, s, K, V);
+        }
         msm_rc_bits<G><<<dim3(nbits * nslice, 1, Wr), 32, 0, st>>>(V, p.half, s, nbits, nslice, Us);
         msm_rc_shift<G><<<dim3(nbits, 1, Wr), 32, 0, st>>>(Us, nbits, nslice, U);
         msm_rc_final<G><<<Wr, 32, 0, st>>>(U, nbits, p.table ? (Pt*)d_out : win);

@@ -159,6 +159,117 @@ __global__ void __launch_bounds__(512) ntt_pass(NttArrays arrs, uint32_t logm, u
     }
 }
 
+// The same pass with TWO stages per shared-memory round trip: a thread holds the four elements of a radix-4 group in
+// registers (same four products as two radix-2 stages, three twiddles), so the pass has half the barriers and half the
+// shared-memory traffic; ncu on ntt_pass showed mio_throttle + barrier stalls holding the IMAD pipe at 55-62 %
+// (profiles/r1_ncu_ntt_pass.txt).  blockDim.x == slots / 4; an odd k ends with one radix-2 stage (two butterflies per thread).
+#ifndef B200_NTT4_MINB
+#define B200_NTT4_MINB 3
+#endif
+template <bool DIF>
+__global__ void __launch_bounds__(256, B200_NTT4_MINB) ntt_pass4(NttArrays arrs, uint32_t logm, uint32_t lo, uint32_t k, uint32_t tb,
+                                                                 const Fr* __restrict__ tw, const Fr* __restrict__ post_scale) {
+    extern __shared__ uint32_t sm[];   // [8][2^k * T]
+    Fr* data = arrs.p[blockIdx.y];
+    const uint32_t T = 1u << tb, tile = 1u << k, slots = tile << tb;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t q0 = blockIdx.x << tb;
+    const uint32_t lomask = (1u << lo) - 1;
+    auto ld = [&](uint32_t s) { Fr x; _Pragma("unroll") for (int i = 0; i < 8; ++i) x.v[i] = sm[i * slots + s]; return x; };
+    auto st = [&](uint32_t s, const Fr& x) { _Pragma("unroll") for (int i = 0; i < 8; ++i) sm[i * slots + s] = x.v[i]; };
+
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint32_t e = tid + r * (slots >> 2);
+        uint32_t mid, tq;
+        if (lo == 0) { mid = e & (tile - 1); tq = e >> k; } else { tq = e & (T - 1); mid = e >> tb; }
+        const uint32_t q = q0 + tq;
+        const size_t addr = ((size_t)(q >> lo) << (lo + k)) | ((size_t)mid << lo) | (q & lomask);
+        st((mid << tb) + tq, data[addr]);
+    }
+    __syncthreads();
+
+    const uint32_t tq = tid & (T - 1), g = tid >> tb;      // g in [0, 2^(k-2))
+    const uint32_t low = (q0 + tq) & lomask;
+    uint32_t l = 0;
+    for (; l + 1 < k; l += 2) {
+        if (DIF) {
+            const uint32_t hb = k - 1 - l, hb2 = hb - 1;
+            const uint32_t r = g & ((1u << hb2) - 1);
+            const uint32_t mid0 = ((g >> hb2) << (hb + 1)) | r;
+            const uint32_t s = (logm - lo - k) + l;
+            const uint32_t s0 = (mid0 << tb) + tq, d1 = (1u << hb2) << tb, d2 = (1u << hb) << tb;
+            Fr e0 = ld(s0), e1 = ld(s0 + d1), e2 = ld(s0 + d2), e3 = ld(s0 + d2 + d1);
+            {   // stage l: (e0, e2), (e1, e3)
+                const Fr wa = tw[((r << lo) | low) << s];
+                const Fr d = (e0 - e2) * wa;
+                e0 = e0 + e2; e2 = d;
+                const Fr wb = tw[(((r + (1u << hb2)) << lo) | low) << s];
+                const Fr f = (e1 - e3) * wb;
+                e1 = e1 + e3; e3 = f;
+            }
+            {   // stage l + 1: (e0, e1), (e2, e3), one twiddle
+                const Fr wc = tw[((r << lo) | low) << (s + 1)];
+                const Fr d = (e0 - e1) * wc;
+                e0 = e0 + e1; e1 = d;
+                const Fr f = (e2 - e3) * wc;
+                e2 = e2 + e3; e3 = f;
+            }
+            st(s0, e0); st(s0 + d1, e1); st(s0 + d2, e2); st(s0 + d2 + d1, e3);
+        } else {
+            const uint32_t r = g & ((1u << l) - 1);
+            const uint32_t mid0 = ((g >> l) << (l + 2)) | r;
+            const uint32_t s = lo + l;
+            const uint32_t s0 = (mid0 << tb) + tq, d1 = (1u << l) << tb, d2 = (2u << l) << tb;
+            Fr e0 = ld(s0), e1 = ld(s0 + d1), e2 = ld(s0 + d2), e3 = ld(s0 + d2 + d1);
+            {   // stage l: (e0, e1), (e2, e3), one twiddle
+                const Fr wa = tw[((r << lo) | low) << (logm - 1 - s)];
+                Fr t = e1 * wa;
+                e1 = e0 - t; e0 = e0 + t;
+                t = e3 * wa;
+                e3 = e2 - t; e2 = e2 + t;
+            }
+            {   // stage l + 1: (e0, e2), (e1, e3)
+                const Fr wb = tw[((r << lo) | low) << (logm - 2 - s)];
+                Fr t = e2 * wb;
+                e2 = e0 - t; e0 = e0 + t;
+                const Fr wc = tw[(((r + (1u << l)) << lo) | low) << (logm - 2 - s)];
+                t = e3 * wc;
+                e3 = e1 - t; e1 = e1 + t;
+            }
+            st(s0, e0); st(s0 + d1, e1); st(s0 + d2, e2); st(s0 + d2 + d1, e3);
+        }
+        __syncthreads();
+    }
+    if (l < k) {      // odd k: one radix-2 stage, two butterflies per thread
+#pragma unroll 1
+        for (uint32_t h = 0; h < 2; ++h) {
+            const uint32_t pi = g + (h << (k - 2));
+            uint32_t hb, e;
+            if (DIF) { hb = k - 1 - l; } else { hb = l; }
+            const uint32_t mid_a = ((pi >> hb) << (hb + 1)) | (pi & ((1u << hb) - 1));
+            if (DIF) e = (((mid_a & ((1u << hb) - 1)) << lo) | low) << ((logm - lo - k) + l);
+            else e = (((mid_a & ((1u << hb) - 1)) << lo) | low) << (logm - 1 - (lo + l));
+            const uint32_t sa = (mid_a << tb) + tq, sb = sa + ((1u << hb) << tb);
+            const Fr a = ld(sa), b = ld(sb), w = tw[e];
+            if (DIF) { st(sa, a + b); st(sb, (a - b) * w); } else { const Fr t = b * w; st(sa, a + t); st(sb, a - t); }
+        }
+        __syncthreads();
+    }
+
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint32_t e = tid + r * (slots >> 2);
+        uint32_t mid, tq2;
+        if (lo == 0) { mid = e & (tile - 1); tq2 = e >> k; } else { tq2 = e & (T - 1); mid = e >> tb; }
+        const uint32_t qq = q0 + tq2;
+        const size_t addr = ((size_t)(qq >> lo) << (lo + k)) | ((size_t)mid << lo) | (qq & lomask);
+        Fr x = ld((mid << tb) + tq2);
+        if (post_scale) x = x * post_scale[addr];
+        data[addr] = x;
+    }
+}
+
 static const uint32_t NTT_KMAX = 8, NTT_SLOTS_LOG = 10;   // up to 2^8-point tiles, 1024 elements (32 KB) per block
 
 static void plan_passes(uint32_t logm, std::vector<uint32_t>& ks) {
@@ -181,6 +292,8 @@ static void run_transform(b200_ctx* ctx, uint32_t logm, Fr* a0, Fr* a1, Fr* a2, 
     if (!attr) {
         B200_CUDA_CHECK(cudaFuncSetAttribute(ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 << NTT_SLOTS_LOG));
         B200_CUDA_CHECK(cudaFuncSetAttribute(ntt_pass<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 << NTT_SLOTS_LOG));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(ntt_pass4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 << NTT_SLOTS_LOG));
+        B200_CUDA_CHECK(cudaFuncSetAttribute(ntt_pass4<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 << NTT_SLOTS_LOG));
         attr = true;
     }
     for (size_t pi = 0; pi < ks.size(); ++pi) {
@@ -190,7 +303,10 @@ static void run_transform(b200_ctx* ctx, uint32_t logm, Fr* a0, Fr* a1, Fr* a2, 
         const uint32_t slots = 1u << (k + tb);
         dim3 grid(1u << (logm - k - tb), n_arr);
         const bool last = (pi + 1 == ks.size());
-        ntt_pass<DIF><<<grid, slots / 2, slots * 32, ctx->stream>>>(arrs, logm, lo, k, tb, tw, last ? post_scale_last : nullptr);
+        if (ctx->ntt_radix4 && k >= 2 && slots >= 128)
+            ntt_pass4<DIF><<<grid, slots / 4, slots * 32, ctx->stream>>>(arrs, logm, lo, k, tb, tw, last ? post_scale_last : nullptr);
+        else
+            ntt_pass<DIF><<<grid, slots / 2, slots * 32, ctx->stream>>>(arrs, logm, lo, k, tb, tw, last ? post_scale_last : nullptr);
         ctx->launches++;
         done += k;
     }

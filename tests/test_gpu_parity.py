@@ -76,6 +76,22 @@ def test_ntt_modes(ctx, logm):
         assert np.array_equal(ctx.ntt(x, logm, 0), orc.dft_naive(x, logm))
 
 
+@pytest.mark.parametrize("logm", [7, 9, 10, 11, 13, 14, 15, 16, 17])
+def test_ntt_radix4_passes(ctx, logm):
+    """ntt_pass4 (two stages per shared-memory round trip; even and odd stage counts per pass, first/middle/last passes)
+    against ntt_pass and the oracle, all four transform kinds."""
+    x = orc.sha512_rng_fr(11 * logm, 1 << logm)
+    for mode in range(4):
+        want = orc.ntt(x, logm, mode)
+        for r4 in (1, 0):
+            ctx.set_option("ntt_radix4", r4)
+            try:
+                got = ctx.ntt(x, logm, mode)
+            finally:
+                ctx.set_option("ntt_radix4", NTT_RADIX4_DEFAULT)
+            assert np.array_equal(got, want), (logm, mode, r4)
+
+
 def test_ntt_large_roundtrip_and_linearity(ctx):
     logm = 20
     n = 1 << logm
@@ -85,6 +101,16 @@ def test_ntt_large_roundtrip_and_linearity(ctx):
     assert np.array_equal(ctx.ntt(ctx.ntt(x, logm, 2), logm, 3), x)
     assert np.array_equal(ctx.ntt(orc.fr_add(x, y), logm, 0), orc.fr_add(fx, ctx.ntt(y, logm, 0)))
     assert np.array_equal(fx, orc.ntt(x, logm, 0))
+    ctx.set_option("ntt_radix4", 1 - NTT_RADIX4_DEFAULT)      # the other pass kernel, full size
+    try:
+        assert np.array_equal(ctx.ntt(x, logm, 0), fx)
+        assert np.array_equal(ctx.ntt(ctx.ntt(x, logm, 2), logm, 3), x)
+    finally:
+        ctx.set_option("ntt_radix4", NTT_RADIX4_DEFAULT)
+
+
+NTT_RADIX4_DEFAULT = 1
+REDUCE_FOLD_DEFAULT = 1
 
 
 def _scalar_mix(n, seed, kind):
@@ -205,6 +231,30 @@ def test_msm_g2_two_dimensional_reduction(ctx):
         finally:
             ctx.set_option("window", 0)
         assert ginf == winf and np.array_equal(got, want), window
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_msm_reduction_stage_b_halving_passes(ctx, group):
+    """msm_rc_fold (stage B of the two-dimensional bucket reduction as halving passes) against the warp-per-output stage B
+    and the oracle: several window sizes (different matrix shapes), windowed and table mode, sparse buckets."""
+    n = 3000
+    fix, omsm = (orc.g1_fixed_base, orc.msm_g1) if group == 1 else (orc.g2_fixed_base, orc.msm_g2)
+    xy, inf = fix(orc.sha512_rng_fr(1 << 47, n))
+    s = _scalar_mix(n, 93, "dense")
+    want, winf = omsm(xy, inf, s)
+    plain, tabled = eb.Bases(ctx, group, xy=xy, inf=inf), eb.Bases(ctx, group, xy=xy, inf=inf)
+    try:
+        for window in (11, 12, 14, 17):
+            tabled.precompute(window)
+            for fold in (2, 0):
+                ctx.set_option("reduce_fold", fold); ctx.set_option("window", window)
+                got, gi = plain.msm(s)
+                assert gi == winf and np.array_equal(got, want), (window, fold, "plain")
+                got, gi = tabled.msm(s)
+                assert gi == winf and np.array_equal(got, want), (window, fold, "tables")
+    finally:
+        ctx.set_option("reduce_fold", REDUCE_FOLD_DEFAULT); ctx.set_option("window", 0)
+        plain.free(); tabled.free()
 
 
 def test_msm_g2_lane_pair_kernel_special_cases(ctx):

@@ -1,11 +1,17 @@
-python -m pytest tests -m gpu -x -q > gpurun_out/r1s13_pytest_gpu.log 2>&1; echo pytest=$?; tail -3 gpurun_out/r1s13_pytest_gpu.log
-python bench.py --steps 20 --warmup 3 > gpurun_out/r1s13_bench.json 2> gpurun_out/r1s13_bench.err; echo bench=$?
-for v in "g2_pair=2" "finalize_chunks=1" "g2_pair=2 finalize_chunks=1"; do
-  o=""; for kv in $v; do o="$o --opt $kv"; done
-  python bench.py --steps 20 --warmup 3 --no-cpu-baseline --mode replicas $o > "gpurun_out/r1s13_bench_$(echo $v | tr ' =' '__').json" 2>> gpurun_out/r1s13_bench.err; echo "variant $v rc=$?"
-done
-for f in gpurun_out/r1s13_bench*.json; do echo $f; python -c "
+python -m pytest tests -m gpu -x -q -k "msm" > gpurun_out/x_pytest_msm.log 2>&1; echo pytest=$?; tail -5 gpurun_out/x_pytest_msm.log
+B="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --mode replicas"
+$B > gpurun_out/x_default.json 2> gpurun_out/x.err; echo rc=$?
+$B --opt reduce_fold=1 > gpurun_out/x_fold.json 2>> gpurun_out/x.err; echo rc=$?
+for f in gpurun_out/x_default.json gpurun_out/x_fold.json; do echo $f; python -c "
 import json,sys
 d=json.loads(open('$f').read().strip().splitlines()[-1])
-print({k:d.get(k) for k in ('value','ms_per_step','e2e','gpu_launches')}); print(d.get('roofline')); print(d.get('phases_ms') or d.get('kernels'))
+print({k:d.get(k) for k in ('value','ms_per_step')}); print(d.get('phases_ms') or d.get('kernels'))
 "; done
+python tools/msm_sweep.py --min 16 --max 20 --g2-max 20 --reps 3 --opt reduce_fold=0 > gpurun_out/x_sweep_nofold.jsonl 2>>gpurun_out/x.err
+python tools/msm_sweep.py --min 16 --max 20 --g2-max 20 --reps 3 --opt reduce_fold=1 > gpurun_out/x_sweep_fold.jsonl 2>>gpurun_out/x.err
+python - <<'P'
+import json
+for f in ('gpurun_out/x_sweep_nofold.jsonl','gpurun_out/x_sweep_fold.jsonl'):
+    for l in open(f):
+        d=json.loads(l); print(f[-14:], d['group'], d['log_n'], round(d['ms'],3), d['in_exponent_ok'], d['phases_ms'].get('msm.reduce'), d['phases_ms'].get('msm.finalize'))
+P
