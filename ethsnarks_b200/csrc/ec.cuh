@@ -111,6 +111,13 @@ struct XYZZ {
         F I = (ZZ * ZZZ).inv();
         return Affine<F>{X * (I * ZZZ), Y * (I * ZZ)};
     }
+    // the same with the binary-Euclid inverse: ~3x lower latency than the 380-product Fermat chain when ONE thread
+    // normalises one point at the very end of a proof (g_finish_kernel), where nothing else hides it
+    B200_DEV Affine<F> to_affine_low_latency() const {
+        if (is_inf()) return Affine<F>::inf();
+        F I = (ZZ * ZZZ).inv_binary();
+        return Affine<F>{X * (I * ZZZ), Y * (I * ZZ)};
+    }
 };
 
 typedef Affine<Fq> G1Affine;

@@ -67,7 +67,7 @@ static int choose_window(size_t n, bool table) {
     return best_c;
 }
 
-static MsmPlan make_plan(b200_ctx* ctx, size_t n, int table_c) {
+static MsmPlan make_plan(b200_ctx* ctx, size_t n, int table_c, bool pair_lanes = false) {
     MsmPlan p;
     int best_c = table_c ? table_c : choose_window(n, false);
     if (ctx->window_override && !table_c) best_c = std::max(4, std::min(24, ctx->window_override));
@@ -79,8 +79,15 @@ static MsmPlan make_plan(b200_ctx* ctx, size_t n, int table_c) {
     p.keybits = 1;
     while ((1ull << p.keybits) <= p.nb) ++p.keybits;   // keys range over [0, nb] (nb = sentinel)
     p.pairs = (uint64_t)n * p.W;
+    // chunk length: ~4 waves of 512 threads per SM, a multiple of 16 pairs (chunks then start on 64-byte boundaries of the
+    // key / value arrays: 2^20 points, 45 -> 48: accumulate 2.28 -> 2.21 ms), and not so short that most runs cross
+    // several chunk edges (measured on B200, G1: 2^18 1.68 -> 1.45 ms at 32, 2^19 2.48 -> 2.25 ms at 48)
     uint64_t L = p.pairs / ((uint64_t)ctx->sm_count * 2048);
-    L = std::max<uint64_t>(16, std::min<uint64_t>(256, L));
+    L = (L + 15) / 16 * 16;
+    L = std::max<uint64_t>(p.pairs >= (6ull << 20) ? 48 : (p.pairs >= (3ull << 19) ? 32 : 16), std::min<uint64_t>(256, L));
+    // the lane-pair G2 kernel runs two threads per chunk, so it fills the SMs with 1.5x longer chunks and pays fewer chunk
+    // edges in the finalize (measured: 2^19 6.09 -> 5.79 ms at 64, 2^20 9.79 -> 9.72 ms at 80)
+    if (pair_lanes && L >= 32) L = std::min<uint64_t>(256, (L * 3 / 2 + 15) / 16 * 16);
     if (ctx->chunk_override) L = ctx->chunk_override;
     p.L = (uint32_t)L;
     p.nchunks = (p.pairs + L - 1) / L;
@@ -110,7 +117,7 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     }
     if (n >= (1ull << 31)) throw std::runtime_error("msm: n must be < 2^31");
     if (table_c && (uint64_t)table_stride * ((255 + table_c - 1) / table_c) >= (1ull << 31)) throw std::runtime_error("msm: table too large for 31-bit point indices");
-    MsmPlan p = make_plan(ctx, n, table_c);
+    MsmPlan p = make_plan(ctx, n, table_c, sizeof(Pt) > 128 && ctx->g2_pair != 0);
     uint32_t* keys0 = (uint32_t*)ctx->scratch("msm_keys0", p.pairs * 4);
     uint32_t* keys1 = (uint32_t*)ctx->scratch("msm_keys1", p.pairs * 4);
     uint32_t* vals0 = (uint32_t*)ctx->scratch("msm_vals0", p.pairs * 4);

@@ -32,7 +32,7 @@ __global__ void g_finish_kernel(const typename G::Pt* xt, int nx, const typename
     Pt r = Pt::inf();
     for (int i = 0; i < nx; ++i) r.add(xt[i]);
     for (int i = 0; i < na; ++i) r.add_mixed(at[i]);
-    typename G::Aff a = r.to_affine();
+    typename G::Aff a = r.to_affine_low_latency();
     uint32_t inf = r.is_inf() ? 1u : 0u;
     if (to_std) {
         // limb-wise from_mont of every Fq coordinate

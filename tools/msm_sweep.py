@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--no-check", action="store_true")
     ap.add_argument("--tables", type=int, default=1)
     ap.add_argument("--chunk", type=int, default=0)
+    ap.add_argument("--table-window", type=int, default=0, help="window size c of the fixed-base tables (0 = cost model)")
     ap.add_argument("--groups", default="1,2")
     ap.add_argument("--affine-rounds", type=int, default=0)
     ap.add_argument("--opt", action="append", default=[], help="library option name=value, repeatable")
@@ -62,7 +63,7 @@ def main():
             lo, hi = shard_range(n, rank, world)
             bases = eb.Bases(ctx, group, scalars=np.ascontiguousarray(k[lo:hi]))
             if args.tables:
-                bases.precompute(0)
+                bases.precompute(args.table_window)
             s_dev = torch.from_numpy(np.ascontiguousarray(s[lo:hi]).view(np.int64)).cuda()
             torch.cuda.synchronize()
             times, sub = [], {}
