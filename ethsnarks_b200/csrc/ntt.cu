@@ -270,7 +270,10 @@ __global__ void __launch_bounds__(256, B200_NTT4_MINB) ntt_pass4(NttArrays arrs,
     }
 }
 
-static const uint32_t NTT_KMAX = 8, NTT_SLOTS_LOG = 10;   // up to 2^8-point tiles, 1024 elements (32 KB) per block
+#ifndef B200_NTT_KMAX
+#define B200_NTT_KMAX 8
+#endif
+static const uint32_t NTT_KMAX = B200_NTT_KMAX, NTT_SLOTS_LOG = 10;   // up to 2^8-point tiles, 1024 elements (32 KB) per block
 
 static void plan_passes(uint32_t logm, std::vector<uint32_t>& ks) {
     ks.clear();

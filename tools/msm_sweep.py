@@ -8,7 +8,7 @@ against the CPU oracle: MSM == (sum k_i s_i) * G.  Prints one JSON line per (gro
 Under torchrun (one process per GPU, NCCL) the (base, scalar) index range is split evenly over the ranks: every
 rank runs the whole window pipeline on its slice, the affine partial sums (8 or 16 limbs + flag per rank) are all-gathered
 and rank 0 adds them.  Timed on the device: max over ranks of the MSM's own CUDA-event time plus the all-gather + additions.
-  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 tools/msm_sweep.py
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 tools/msm_sweep.py --from 20 --to 26
 """
 import argparse
 import json
@@ -26,8 +26,8 @@ from bench import rand_scalars, shard_range, max_over_ranks, MAC_PER_G1_POINT, M
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--min", type=int, default=16)
-    ap.add_argument("--max", type=int, default=24)
+    ap.add_argument("--min", "--from", dest="min", type=int, default=16)
+    ap.add_argument("--max", "--to", dest="max", type=int, default=24, help="--from/--to: the same under torchrun, whose own parser claims --max")
     ap.add_argument("--g2-max", type=int, default=22)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--no-check", action="store_true")
@@ -68,6 +68,11 @@ def main():
             torch.cuda.synchronize()
             times, sub = [], {}
             limbs = 8 if group == 1 else 16
+            if world > 1:
+                pin = torch.zeros(limbs + 1, dtype=torch.int64).pin_memory()
+                pin_np = pin.numpy().view(np.uint64)
+                mine = torch.zeros(limbs + 1, dtype=torch.int64, device="cuda")
+                allp = torch.zeros(world * (limbs + 1), dtype=torch.int64, device="cuda")
             for r in range(args.reps + 1):
                 if world > 1:
                     dist.barrier()
@@ -75,21 +80,24 @@ def main():
                 t = dict(ctx.timings())
                 if world > 1:
                     # the one exchange step: all ranks' affine partial sums, then <= world - 1 additions
-                    part = np.zeros(limbs + 1, dtype=np.uint64)
+                    part = pin_np
                     part[:limbs] = np.asarray(got).reshape(-1)
                     part[limbs] = int(np.asarray(inf).reshape(-1)[0])
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    pin = torch.from_numpy(part.view(np.int64)).pin_memory()
                     e0.record()
-                    mine = pin.cuda(non_blocking=True)
-                    allp = [torch.empty_like(mine) for _ in range(world)]
-                    dist.all_gather(allp, mine)
-                    host = torch.stack(allp).cpu().numpy().view(np.uint64)
-                    got, inf = host[0, :limbs].copy(), np.array([host[0, limbs]], dtype=np.uint8)
+                    mine.copy_(pin, non_blocking=True)
+                    dist.all_gather_into_tensor(allp, mine)
+                    host = allp.cpu().numpy().view(np.uint64).reshape(world, limbs + 1)
+                    pts = np.ascontiguousarray(host[:, :limbs])
+                    flg = np.ascontiguousarray(host[:, limbs].astype(np.uint8))
                     add = ctx.g1_add if group == 1 else ctx.g2_add
-                    for q in range(1, world):
-                        got, inf = add(got.reshape(1, limbs), inf, host[q, :limbs].reshape(1, limbs).copy(),
-                                       np.array([host[q, limbs]], dtype=np.uint8))
+                    while len(pts) > 1:                      # pairwise rounds: log2(world) batched additions
+                        h = len(pts) // 2
+                        a, ai = add(pts[:h], flg[:h], pts[h:2 * h], flg[h:2 * h])
+                        if len(pts) & 1:
+                            a, ai = np.concatenate([a, pts[2 * h:]]), np.concatenate([ai, flg[2 * h:]])
+                        pts, flg = np.ascontiguousarray(a), np.ascontiguousarray(ai)
+                    got, inf = pts[0], flg[:1]
                     got = np.asarray(got).reshape(-1)
                     e1.record()
                     torch.cuda.synchronize()
