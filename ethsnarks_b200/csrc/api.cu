@@ -189,6 +189,7 @@ int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
     for (int i = 1; i < 4; ++i) cudaStreamCreateWithPriority(&c->lanes[i], cudaStreamNonBlocking, prio(lv[i]));
     for (int i = 0; i < 4; ++i) cudaEventCreateWithFlags(&c->lane_done[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_witness, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_shared, cudaEventDisableTiming);
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
     *out = c;
@@ -203,6 +204,7 @@ void b200_shutdown(b200_ctx* ctx) {
     for (int i = 1; i < 4; ++i) cudaStreamDestroy(ctx->lanes[i]);
     for (int i = 0; i < 4; ++i) cudaEventDestroy(ctx->lane_done[i]);
     cudaEventDestroy(ctx->ev_witness);
+    cudaEventDestroy(ctx->ev_shared);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -219,6 +221,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "reduce_1d")) ctx->reduce_1d = (int)value;
     else if (!strcmp(name, "g2_pair")) ctx->g2_pair = (int)value;
     else if (!strcmp(name, "ntt_radix4")) ctx->ntt_radix4 = (int)value;
+    else if (!strcmp(name, "shared_sort")) ctx->shared_sort = (int)value;
     else if (!strcmp(name, "reduce_fold")) ctx->reduce_fold = (int)value;
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
     else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;
@@ -279,6 +282,24 @@ int b200_g1_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const
 int b200_g2_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf, uint64_t* out_xy,
                 uint8_t* out_inf, size_t n) {
     return group_add(ctx, 2, a_xy, a_inf, b_xy, b_inf, out_xy, out_inf, n);
+}
+
+// sum of n affine points in one kernel (the "reduce" of SURVEY 8e: the all-gathered per-GPU partial sums of a sharded MSM)
+static int group_sum(b200_ctx* ctx, int group, const uint64_t* xy, const uint8_t* inf, size_t n, uint64_t* out_xy, uint8_t* out_inf) {
+    if (!ctx || (!xy && n) || !out_xy || !out_inf || n > (1u << 20)) return B200_ERR_ARG;
+    return Guard{ctx}.run([&] {
+        DevBuf d(std::max<size_t>(1, n) * aff_bytes(group)), fin(aff_bytes(group) + 256);
+        upload_points(ctx, group, xy, inf, n, d.p);
+        g_finish(ctx, group, nullptr, 0, d.p, (int)n, fin.p, false);
+        fetch_finished(ctx, group, fin.p, out_xy, out_inf);
+        return (int)B200_OK;
+    });
+}
+int b200_g1_sum(b200_ctx* ctx, const uint64_t* xy, const uint8_t* inf, size_t n, uint64_t* out_xy, uint8_t* out_inf) {
+    return group_sum(ctx, 1, xy, inf, n, out_xy, out_inf);
+}
+int b200_g2_sum(b200_ctx* ctx, const uint64_t* xy, const uint8_t* inf, size_t n, uint64_t* out_xy, uint8_t* out_inf) {
+    return group_sum(ctx, 2, xy, inf, n, out_xy, out_inf);
 }
 
 static int fixed_base(b200_ctx* ctx, int group, const uint64_t* scalars, size_t n, uint64_t* out_xy, uint8_t* out_inf) {

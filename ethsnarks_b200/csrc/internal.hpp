@@ -32,6 +32,9 @@ struct b200_ctx {
                                        // 1 = strict, 3 = lazy + out-of-line products; 0 = one thread per point
     int finalize_chunks = 1;           // 1 = stitch chunk partial sums with one thread per chunk edge (msm_finalize_chunks)
     int ntt_radix4 = 1;                // 1 = NTT passes with two stages per shared-memory round trip (ntt_pass4)
+    int shared_sort = 1;               // 1 = the witness MSMs of one prove (A, B, L) consume ONE sorted digit list when their
+                                       // queries are dense and their tables share a window size
+    cudaEvent_t ev_shared = nullptr;
     int reduce_fold = 1;               // stage B of the 2D bucket reduction as halving passes (msm_rc_fold): 1 = for bucket sets of
                                        // >= 2^17 (measured: pays from there on, costs ~20 us of extra launches below), 2 = always, 0 = never
     int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one
@@ -62,6 +65,25 @@ struct b200_ctx {
 
 namespace b200 {
 
+// A sorted digit list that several MSMs over the SAME scalars consume (one prove: A, B in G2 [and G1] and L all multiply the
+// witness): digits, sort and offsets run once instead of once per query.  The list is over scalar (variable) indices -
+// value = sign << 31 | window << 26 | variable.  Each consumer rewrites the values into its own table indices in one
+// streaming pass (msm_translate: 8 B per pair against three 16 B radix passes): a variable maps to a table position through
+// MsmPos (inverse index list of a sparse query, or an index range); a variable the query does not hold points at the
+// all-zero entry appended to the table, i.e. the point at infinity, which every accumulate kernel skips.
+struct MsmShared {
+    int c = 0;
+    uint32_t n = 0;                 // scalars in the list
+    const uint32_t* keys = nullptr;
+    const uint32_t* vals = nullptr;
+    const uint64_t* offsets = nullptr;
+};
+struct MsmPos {
+    const uint32_t* map;            // variable -> position in the query, 0xffffffff = absent; nullptr = the range [off, off + count)
+    uint32_t off, count, stride;    // stride = table stride (entries per window); the zero entry sits at index W * stride
+};
+#define B200_SHARED_VAR_BITS 26
+
 // --- msm.cu ---------------------------------------------------------------------------------------------------
 // Device-resident inputs; result is ONE XYZZ point written to d_out (G1: 4x32 B, G2: 4x64 B).
 //   group: 1 = G1, 2 = G2.  d_scalars: Fr elements (Montgomery if scalars_mont, else standard form), optionally
@@ -77,6 +99,11 @@ namespace b200 {
     void g_scalar_mul_##SUFFIX(b200_ctx* ctx, const void* d_affine_base, const void* d_scalar_mont, void* d_out_xyzz);
 B200_DECL_GROUP(g1)
 B200_DECL_GROUP(g2)
+// shared list: digits + sort + offsets of n Montgomery scalars for window size c on the current lane (table mode), then one
+// consume per query on any lane that has waited for the prepare
+void msm_shared_prepare(b200_ctx* ctx, const void* d_scalars_mont, size_t n, int c, MsmShared* out);
+void msm_shared_consume_g1(b200_ctx* ctx, const MsmShared& sh, const void* d_table, MsmPos pos, void* d_out_xyzz);
+void msm_shared_consume_g2(b200_ctx* ctx, const MsmShared& sh, const void* d_table, MsmPos pos, void* d_out_xyzz);
 // g_finish: out = sum(xyzz terms) + sum(affine terms) normalised to affine (Montgomery, or standard form if to_std),
 //           written as the affine point followed by a u32 infinity flag.
 // table_c != 0: d_bases is a window table (table[w * table_stride + i] = 2^(table_c w) P_i) built by g_precompute

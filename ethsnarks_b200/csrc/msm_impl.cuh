@@ -10,7 +10,7 @@ namespace b200 {
 template <bool MONT>
 static __global__ void __launch_bounds__(256) msm_digits(const Fr* __restrict__ scalars, const uint32_t* __restrict__ gather, uint32_t n,
                                                   int c, int W, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
-                                                  uint32_t stride, int table) {
+                                                  uint32_t stride, int table, int packed) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     Fr s = scalars[gather ? gather[i] : i];
@@ -33,7 +33,7 @@ static __global__ void __launch_bounds__(256) msm_digits(const Fr* __restrict__ 
         uint32_t u = raw + carry, d, neg;
         if (u > half) { d = full - u; neg = 1; carry = 1; } else { d = u; neg = 0; carry = 0; }
         keys[(size_t)w * n + i] = d ? (table ? 0u : (uint32_t)w * half) + d - 1 : sentinel;
-        vals[(size_t)w * n + i] = (table ? (uint32_t)w * stride + i : i) | (neg << 31);
+        vals[(size_t)w * n + i] = (packed ? ((uint32_t)w << B200_SHARED_VAR_BITS) | i : table ? (uint32_t)w * stride + i : i) | (neg << 31);
     }
 }
 
@@ -102,40 +102,23 @@ static MsmPlan make_plan(b200_ctx* ctx, size_t n, int table_c, bool pair_lanes =
 template <typename Pt>
 static __global__ void msm_set_inf(Pt* out) { *out = Pt::inf(); }
 
-template <typename G>
-static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_gather, size_t n, bool scalars_mont,
-                      void* d_out, int table_c, size_t table_stride) {
-    typedef typename G::Pt Pt;
-    typedef typename G::Aff Aff;
-    cudaStream_t st = ctx->cur();
-    if (n == 0) {
-        // empty sum = infinity
-        Pt* out = (Pt*)d_out;
-        msm_set_inf<Pt><<<1, 1, 0, st>>>(out);
-        ctx->launches++;
-        return;
-    }
-    if (n >= (1ull << 31)) throw std::runtime_error("msm: n must be < 2^31");
-    if (table_c && (uint64_t)table_stride * ((255 + table_c - 1) / table_c) >= (1ull << 31)) throw std::runtime_error("msm: table too large for 31-bit point indices");
-    MsmPlan p = make_plan(ctx, n, table_c, sizeof(Pt) > 128 && ctx->g2_pair != 0);
-    uint32_t* keys0 = (uint32_t*)ctx->scratch("msm_keys0", p.pairs * 4);
-    uint32_t* keys1 = (uint32_t*)ctx->scratch("msm_keys1", p.pairs * 4);
-    uint32_t* vals0 = (uint32_t*)ctx->scratch("msm_vals0", p.pairs * 4);
-    uint32_t* vals1 = (uint32_t*)ctx->scratch("msm_vals1", p.pairs * 4);
-    uint64_t* offsets = (uint64_t*)ctx->scratch("msm_offsets", ((size_t)p.nb + 2) * 8);
-    Pt* buckets = (Pt*)ctx->scratch("msm_buckets", (size_t)p.nb * sizeof(Pt));
-    Pt* pfirst = (Pt*)ctx->scratch("msm_pfirst", p.nchunks * sizeof(Pt));
-    Pt* plast = (Pt*)ctx->scratch("msm_plast", p.nchunks * sizeof(Pt));
-    const size_t big_cap = p.nchunks / B200_BIG_SPAN + 2;
-    uint32_t* big = (uint32_t*)ctx->scratch("msm_big", (big_cap + 1) * 4);
-    Pt* seg = (Pt*)ctx->scratch("msm_seg", ((size_t)p.nseg * p.W + p.nseg / 64 + 64) * sizeof(Pt));
-    Pt* win = (Pt*)ctx->scratch("msm_win", (size_t)p.W * sizeof(Pt));
-
+// stages 1-3: digits, sort, offsets.  `tag` selects the scratch set (the shared list must survive the consumers' own scratch).
+struct MsmSorted { const uint32_t* keys; const uint32_t* vals; uint64_t* offsets; };
+static MsmSorted msm_sort_stage(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void* d_scalars, const uint32_t* d_gather, size_t n,
+                                bool scalars_mont, size_t table_stride, bool packed) {
+    const char* nm[6] = {"msm_keys0", "msm_keys1", "msm_vals0", "msm_vals1", "msm_offsets", "msm_sort_tmp"};
+    const char* nms[6] = {"msm_sh_keys0", "msm_sh_keys1", "msm_sh_vals0", "msm_sh_vals1", "msm_sh_offsets", "msm_sh_sort_tmp"};
+    const char** names = packed ? nms : nm;
+    uint32_t* keys0 = (uint32_t*)ctx->scratch(names[0], p.pairs * 4);
+    uint32_t* keys1 = (uint32_t*)ctx->scratch(names[1], p.pairs * 4);
+    uint32_t* vals0 = (uint32_t*)ctx->scratch(names[2], p.pairs * 4);
+    uint32_t* vals1 = (uint32_t*)ctx->scratch(names[3], p.pairs * 4);
+    uint64_t* offsets = (uint64_t*)ctx->scratch(names[4], ((size_t)p.nb + 2) * 8);
     ctx->t_begin("msm.digits");
     {
         dim3 grid((unsigned)((n + 255) / 256));
-        if (scalars_mont) msm_digits<true><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0, (uint32_t)table_stride, p.table);
-        else msm_digits<false><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0, (uint32_t)table_stride, p.table);
+        if (scalars_mont) msm_digits<true><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0, (uint32_t)table_stride, p.table, packed);
+        else msm_digits<false><<<grid, 256, 0, st>>>((const Fr*)d_scalars, d_gather, (uint32_t)n, p.c, p.W, keys0, vals0, (uint32_t)table_stride, p.table, packed);
         ctx->launches++;
     }
     ctx->t_end();
@@ -144,33 +127,39 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     {
         size_t tmp_bytes = 0;
         B200_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, p.pairs, 0, p.keybits, st));
-        void* tmp = ctx->scratch("msm_sort_tmp", tmp_bytes);
+        void* tmp = ctx->scratch(names[5], tmp_bytes);
         B200_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, kb, vb, p.pairs, 0, p.keybits, st));
     }
-    const uint32_t* skeys = kb.Current();
-    const uint32_t* svals = vb.Current();
     ctx->t_end();
     ctx->t_begin("msm.offsets");
-    msm_offsets<<<(p.nb + 1 + 255) / 256, 256, 0, st>>>(skeys, p.pairs, p.nb, offsets);
+    msm_offsets<<<(p.nb + 1 + 255) / 256, 256, 0, st>>>(kb.Current(), p.pairs, p.nb, offsets);
     ctx->launches++;
     ctx->t_end();
-    // batched-affine pre-reduction: R rounds leave runs 2^R times shorter for the XYZZ accumulate
-    int rounds = ctx->affine_rounds;
-    if (rounds < 0) {
-        const double avg_run = (double)p.pairs / (double)p.nb;
-        rounds = 0;
-        while (rounds < 4 && avg_run >= (double)(8 << rounds)) ++rounds;      // keep >= ~4 per run for the accumulate
-    }
-    const uint32_t* akeys = skeys;
-    const uint32_t* avals = svals;
-    const void* abases = d_bases;
-    const uint64_t* aoff = offsets;
-    if (rounds > 0) {
-        ctx->t_begin("msm.affine");
-        launch_affine_rounds<G>(ctx, st, p, rounds, skeys, svals, d_bases, offsets, &akeys, &abases, &aoff);
-        avals = nullptr;
-        ctx->t_end();
-    }
+    return MsmSorted{kb.Current(), vb.Current(), offsets};
+}
+
+// shared list -> one consumer's values (internal.hpp: MsmShared)
+static __global__ void __launch_bounds__(256) msm_translate(const uint32_t* __restrict__ vals, uint64_t pairs, MsmPos pos, uint32_t zero_index,
+                                                            uint32_t* __restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pairs) return;
+    const uint32_t v = vals[i], idx = v & 0x7fffffffu, var = idx & ((1u << B200_SHARED_VAR_BITS) - 1);
+    const uint32_t ps = pos.map ? pos.map[var] : var - pos.off;
+    out[i] = ps < pos.count ? (v & 0x80000000u) | ((idx >> B200_SHARED_VAR_BITS) * pos.stride + ps) : zero_index;
+}
+
+// stages 4-6: accumulate, finalize, reduce over a sorted list
+template <typename G>
+static void msm_tail(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* akeys, const uint32_t* avals, const uint64_t* aoff,
+                     const void* abases, void* d_out) {
+    typedef typename G::Pt Pt;
+    Pt* buckets = (Pt*)ctx->scratch("msm_buckets", (size_t)p.nb * sizeof(Pt));
+    Pt* pfirst = (Pt*)ctx->scratch("msm_pfirst", p.nchunks * sizeof(Pt));
+    Pt* plast = (Pt*)ctx->scratch("msm_plast", p.nchunks * sizeof(Pt));
+    const size_t big_cap = p.nchunks / B200_BIG_SPAN + 2;
+    uint32_t* big = (uint32_t*)ctx->scratch("msm_big", (big_cap + 1) * 4);
+    Pt* seg = (Pt*)ctx->scratch("msm_seg", ((size_t)p.nseg * p.W + p.nseg / 64 + 64) * sizeof(Pt));
+    Pt* win = (Pt*)ctx->scratch("msm_win", (size_t)p.W * sizeof(Pt));
     ctx->t_begin("msm.accumulate");
     launch_accumulate<G>(ctx, st, p, akeys, avals, aoff, abases, buckets, pfirst, plast);
     ctx->t_end();
@@ -183,11 +172,64 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     B200_CUDA_CHECK(cudaGetLastError());
 }
 
+template <typename G>
+static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_gather, size_t n, bool scalars_mont,
+                      void* d_out, int table_c, size_t table_stride) {
+    typedef typename G::Pt Pt;
+    cudaStream_t st = ctx->cur();
+    if (n == 0) {
+        // empty sum = infinity
+        Pt* out = (Pt*)d_out;
+        msm_set_inf<Pt><<<1, 1, 0, st>>>(out);
+        ctx->launches++;
+        return;
+    }
+    if (n >= (1ull << 31)) throw std::runtime_error("msm: n must be < 2^31");
+    if (table_c && (uint64_t)table_stride * ((255 + table_c - 1) / table_c) >= (1ull << 31)) throw std::runtime_error("msm: table too large for 31-bit point indices");
+    MsmPlan p = make_plan(ctx, n, table_c, sizeof(Pt) > 128 && ctx->g2_pair != 0);
+    const MsmSorted so = msm_sort_stage(ctx, st, p, d_scalars, d_gather, n, scalars_mont, table_stride, false);
+    // batched-affine pre-reduction: R rounds leave runs 2^R times shorter for the XYZZ accumulate
+    int rounds = ctx->affine_rounds;
+    if (rounds < 0) {
+        const double avg_run = (double)p.pairs / (double)p.nb;
+        rounds = 0;
+        while (rounds < 4 && avg_run >= (double)(8 << rounds)) ++rounds;      // keep >= ~4 per run for the accumulate
+    }
+    const uint32_t* akeys = so.keys;
+    const uint32_t* avals = so.vals;
+    const void* abases = d_bases;
+    const uint64_t* aoff = so.offsets;
+    if (rounds > 0) {
+        ctx->t_begin("msm.affine");
+        launch_affine_rounds<G>(ctx, st, p, rounds, so.keys, so.vals, d_bases, so.offsets, &akeys, &abases, &aoff);
+        avals = nullptr;
+        ctx->t_end();
+    }
+    msm_tail<G>(ctx, st, p, akeys, avals, aoff, abases, d_out);
+}
+
+// One MSM of a shared list (internal.hpp: MsmShared) against this group's window table (W * stride entries + the zero entry).
+template <typename G>
+static void msm_shared_consume_t(b200_ctx* ctx, const MsmShared& sh, const void* d_table, MsmPos pos, void* d_out) {
+    typedef typename G::Pt Pt;
+    cudaStream_t st = ctx->cur();
+    MsmPlan p = make_plan(ctx, sh.n, sh.c, sizeof(Pt) > 128 && ctx->g2_pair != 0);
+    if ((uint64_t)p.W * pos.stride + 1 >= (1ull << 31)) throw std::runtime_error("msm: table too large for 31-bit point indices");
+    uint32_t* tvals = (uint32_t*)ctx->scratch("msm_sh_tvals", p.pairs * 4);
+    ctx->t_begin("msm.translate");
+    msm_translate<<<(unsigned)((p.pairs + 255) / 256), 256, 0, st>>>(sh.vals, p.pairs, pos, (uint32_t)p.W * pos.stride, tvals);
+    ctx->launches++;
+    ctx->t_end();
+    msm_tail<G>(ctx, st, p, sh.keys, tvals, sh.offsets, d_table, d_out);
+}
 
 #define B200_INSTANTIATE_GROUP_RUN(G, SUFFIX)                                                                                          \
     void msm_run_##SUFFIX(b200_ctx* ctx, const void* b, const void* s, const uint32_t* g, size_t n, bool mont, void* out, int tc,     \
                           size_t ts) {                                                                                                 \
         msm_run_t<G>(ctx, b, s, g, n, mont, out, tc, ts);                                                                              \
+    }                                                                                                                                  \
+    void msm_shared_consume_##SUFFIX(b200_ctx* ctx, const MsmShared& sh, const void* table, MsmPos pos, void* out) {                   \
+        msm_shared_consume_t<G>(ctx, sh, table, pos, out);                                                                             \
     }
 
 }  // namespace b200

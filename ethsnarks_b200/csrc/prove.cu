@@ -33,6 +33,8 @@ struct b200_key {
     uint64_t H_lo = 0;          // first (bit-reversed) H position held by this rank
     void *A = nullptr, *B2 = nullptr, *B1 = nullptr, *H = nullptr, *L = nullptr;
     uint32_t *A_idx = nullptr, *B_idx = nullptr;
+    uint32_t *A_pos = nullptr, *B_pos = nullptr;   // variable -> entry of the A / B query (0xffffffff = absent): shared digit list
+    bool A_ident = false, B_ident = false;         // the query's index list is 0, 1, 2, ...: no map needed
     // fixed-base window tables (built at circuit_load when ctx->precompute): [W][n] affine, window size per query
     void *A_t = nullptr, *B2_t = nullptr, *B1_t = nullptr, *H_t = nullptr, *L_t = nullptr;
     int cA = 0, cB = 0, cH = 0, cL = 0;
@@ -134,7 +136,7 @@ void key_release(b200_key* k) {
     if (k->owns_bases) { cudaFree(k->A); cudaFree(k->B2); cudaFree(k->B1); cudaFree(k->L); }
     cudaFree(k->H);
     cudaFree(k->A_t); cudaFree(k->B2_t); cudaFree(k->B1_t); cudaFree(k->H_t); cudaFree(k->L_t);
-    cudaFree(k->A_idx); cudaFree(k->B_idx); cudaFree(k->consts_g1); cudaFree(k->consts_g2);
+    cudaFree(k->A_idx); cudaFree(k->B_idx); cudaFree(k->A_pos); cudaFree(k->B_pos); cudaFree(k->consts_g1); cudaFree(k->consts_g2);
     for (int i = 0; i < 3; ++i) csr_free(&k->M[i]);
     cudaFree(k->coeffs);
     if (k->has_circuit) domain_free(&k->dom);
@@ -166,15 +168,46 @@ void build_table(b200_key* k, int group, const void* pts, uint64_t n, void** tab
     if (!k->ctx->precompute || !n || !pts) return;
     const int win = k->ctx->window_override ? std::max(4, std::min(24, k->ctx->window_override)) : msm_table_window(n);
     const int W = (255 + win - 1) / win;
-    const size_t bytes = (size_t)W * n * (group == 1 ? 64 : 128);
+    const size_t esz = group == 1 ? 64 : 128;
+    const size_t bytes = (size_t)W * n * esz + esz;      // + one all-zero entry (infinity) for the shared digit list
     size_t free_b = 0, total_b = 0;
     B200_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
     if (bytes + (8ull << 30) > free_b) return;   // does not fit beside the MSM scratch: stay on the windowed path
     B200_CUDA_CHECK(cudaMalloc(table, bytes));
+    B200_CUDA_CHECK(cudaMemsetAsync((char*)*table + bytes - esz, 0, esz, k->ctx->stream));
     g_precompute(k->ctx, group, pts, n, win, *table);
     *c = win;
 }
+__global__ void pos_scatter_kernel(const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ pos, uint32_t nvar) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && idx[i] < nvar) pos[idx[i]] = i;
+}
+// inverse of a query's variable index list, for the shared digit list of the witness MSMs (msm_common.cuh: MsmShared)
+__global__ void idx_not_identity_kernel(const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ flag) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && idx[i] != i) *flag = 1u;
+}
+void build_pos_map(b200_key* k, const uint32_t* idx, uint64_t n, uint32_t** pos, bool* ident) {
+    cudaFree(*pos);
+    *pos = nullptr;
+    *ident = false;
+    const uint64_t nvar = k->nv + 1;
+    if (!idx || !n || k->world != 1 || nvar >= (1ull << B200_SHARED_VAR_BITS)) return;
+    B200_CUDA_CHECK(cudaMalloc(pos, nvar * 4));
+    B200_CUDA_CHECK(cudaMemsetAsync(*pos, 0xff, nvar * 4, k->ctx->stream));
+    pos_scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, k->ctx->stream>>>(idx, (uint32_t)n, *pos, (uint32_t)nvar);
+    uint32_t* flag = (uint32_t*)k->ctx->scratch("pos_flag", 4);
+    B200_CUDA_CHECK(cudaMemsetAsync(flag, 0, 4, k->ctx->stream));
+    idx_not_identity_kernel<<<(unsigned)((n + 255) / 256), 256, 0, k->ctx->stream>>>(idx, (uint32_t)n, flag);
+    k->ctx->launches += 2;
+    uint32_t h = 1;
+    B200_CUDA_CHECK(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, k->ctx->stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(k->ctx->stream));
+    *ident = (h == 0);
+}
 void build_tables(b200_key* k) {
+    build_pos_map(k, k->A_idx, k->nA, &k->A_pos, &k->A_ident);
+    build_pos_map(k, k->B_idx, k->nB, &k->B_pos, &k->B_ident);
     build_table(k, 1, k->A, k->nA, &k->A_t, &k->cA);
     build_table(k, 2, k->B2, k->nB, &k->B2_t, &k->cB);
     if (k->full) { int cb1 = 0; build_table(k, 1, k->B1, k->nB, &k->B1_t, &cb1); if (cb1 != k->cB) { cudaFree(k->B1_t); k->B1_t = nullptr; } }
@@ -638,6 +671,38 @@ void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1, int finish =
         if (ctx->lane) B200_CUDA_CHECK(cudaEventRecord(ctx->lane_done[ctx->lane], ctx->lanes[ctx->lane]));
         ctx->lane = 0;
     };
+    // One sorted digit list for all of them when every query is dense over the variables and the tables share a window
+    // size: digits + sort + offsets run once (on the G2 lane) instead of three or four times.
+    const uint64_t nvar = k->nv + 1;
+    const bool share = ctx->shared_sort && ctx->affine_rounds == 0 && k->world == 1 && k->A_t && k->B2_t && k->L_t && k->A_pos && k->B_pos &&
+                       k->cA == k->cB && k->cA == k->cL && k->cA >= 8 /* <= 32 windows */ && (!want_b1 || k->B1_t) && nvar < (1ull << B200_SHARED_VAR_BITS) &&
+                       5 * k->nA >= 4 * nvar && 5 * k->nB >= 4 * nvar && 5 * k->nL >= 4 * nvar;
+    if (share) {
+        try {
+            MsmShared sh;
+            lane_begin(1, "msm.B_g2");
+            ctx->t_begin("msm.shared_sort");
+            msm_shared_prepare(ctx, k->d_w, nvar, k->cA, &sh);
+            ctx->t_end();
+            if (ctx->lane) B200_CUDA_CHECK(cudaEventRecord(ctx->ev_shared, ctx->lanes[ctx->lane]));
+            msm_shared_consume_g2(ctx, sh, k->B2_t, MsmPos{k->B_ident ? nullptr : k->B_pos, 0, (uint32_t)k->nB, (uint32_t)k->nB}, a.B2);
+            if (finish == 1) g_finish(ctx, 2, a.B2, 1, k->consts_g2, 1, fin + 256, true);
+            if (finish == 2) g_finish(ctx, 2, a.B2, 1, nullptr, 0, fin + 256, false);
+            lane_end();
+            lane_begin(2, "msm.A");
+            if (ctx->lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->lanes[ctx->lane], ctx->ev_shared, 0));
+            msm_shared_consume_g1(ctx, sh, k->A_t, MsmPos{k->A_ident ? nullptr : k->A_pos, 0, (uint32_t)k->nA, (uint32_t)k->nA}, a.A);
+            if (want_b1) msm_shared_consume_g1(ctx, sh, k->B1_t, MsmPos{k->B_ident ? nullptr : k->B_pos, 0, (uint32_t)k->nB, (uint32_t)k->nB}, a.B1);
+            if (finish == 1) g_finish(ctx, 1, a.A, 1, k->consts_g1, 1, fin, true);
+            if (finish == 2) g_finish(ctx, 1, a.A, 1, nullptr, 0, fin, false);
+            lane_end();
+            lane_begin(3, "msm.L");
+            if (ctx->lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->lanes[ctx->lane], ctx->ev_shared, 0));
+            msm_shared_consume_g1(ctx, sh, k->L_t, MsmPos{nullptr, (uint32_t)(k->ni + 1 + k->L_lo), (uint32_t)k->nL, (uint32_t)k->nL}, a.L);
+            lane_end();
+        } catch (...) { ctx->lane = 0; throw; }
+        return;
+    }
     try {
         lane_begin(1, "msm.B_g2");
         msm_run(ctx, 2, k->B2_t ? k->B2_t : k->B2, k->d_w, k->B_idx, k->nB, true, a.B2, k->B2_t ? k->cB : 0, k->nB);

@@ -28,7 +28,7 @@ SYMBOLS = [
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
     "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
-    "b200_generate_key",
+    "b200_generate_key", "b200_g1_sum", "b200_g2_sum",
 ]
 
 
@@ -159,6 +159,22 @@ class Context:
 
     def g2_add(self, a, ai, b, bi):
         return self._gadd(self.lib.b200_g2_add, 16, a, ai, b, bi)
+
+    def _gsum(self, fn, w, xy, inf):
+        xy = _arr(xy)
+        n = xy.size // w
+        inf = _arr(inf, np.uint8) if inf is not None else np.zeros(n, np.uint8)
+        out = np.zeros(w, np.uint64)
+        oi = C.c_uint8(0)
+        self.check(fn(self.h, _p64(xy), inf.ctypes.data_as(u8p), C.c_size_t(n), _p64(out), C.byref(oi)), "group sum")
+        return out, oi.value
+
+    def g1_sum(self, xy, inf=None):
+        """sum of n affine G1 points (n x 8 Montgomery limbs) -> (8 limbs, infinity flag)"""
+        return self._gsum(self.lib.b200_g1_sum, 8, xy, inf)
+
+    def g2_sum(self, xy, inf=None):
+        return self._gsum(self.lib.b200_g2_sum, 16, xy, inf)
 
     def _fixed(self, fn, w, scalars):
         s = _arr(scalars)

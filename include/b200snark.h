@@ -61,7 +61,20 @@ const char* b200_strerror(int code);
 const char* b200_last_error(b200_ctx* ctx);
 void* b200_stream(b200_ctx* ctx);                        /* the cudaStream_t every kernel of this ctx is launched on */
 unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by this library on ctx since b200_init */
-int b200_set_option(b200_ctx* ctx, const char* name, long value);   /* "window" (Config::multi_exp_c), "chunk", "timing", "precompute", "overlap", "reduce_1d", "affine_rounds", "g2_pair", "finalize_chunks" */
+/* Tuning knobs; every setting gives the same results (tests run the alternatives against each other and the oracle).
+ *   "window"          c of the windowed MSM and of tables built afterwards; 0 = cost model (libsnark::Config::multi_exp_c)
+ *   "chunk"           pairs per accumulate thread; 0 = by size
+ *   "precompute"      1 = fixed-base window tables for resident keys / base sets (default), 0 = plain windowed path
+ *   "overlap"         1 = the MSMs of one prove on separate lanes (default), 0 = serialised (per-kernel timing)
+ *   "timing"          1 = record CUDA-event phase timings (default)
+ *   "g2_pair"         G2 accumulate: 2 = one point per lane pair, lazy operand forms (default), 1 = strict forms,
+ *                     3 = lazy + out-of-line products, 0 = one thread per point
+ *   "finalize_chunks" 1 = stitch chunk partial sums with one thread per chunk edge (default), 0 = one per bucket
+ *   "reduce_fold"     stage B of the bucket reduction as halving passes: 1 = for >= 2^17 buckets (default), 2 = always, 0 = never
+ *   "reduce_1d"       1 = running-sum bucket reduction instead of the two-dimensional one
+ *   "ntt_radix4"      1 = NTT passes with two stages per shared-memory round trip (default), 0 = one
+ *   "affine_rounds"   batched-affine pre-reduction rounds before the accumulate (0 = off, default; -1 = by run length) */
+int b200_set_option(b200_ctx* ctx, const char* name, long value);
 int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
 int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);
 int b200_timing_start(b200_ctx* ctx, int i, float* ms);  /* start of phase i relative to the first phase of the call */
@@ -76,6 +89,10 @@ int b200_g1_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const
                 uint64_t* out_xy, uint8_t* out_inf, size_t n);
 int b200_g2_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const uint64_t* b_xy, const uint8_t* b_inf,
                 uint64_t* out_xy, uint8_t* out_inf, size_t n);
+/* sum of n affine points (Montgomery limbs, optional infinity flags) in one kernel, normalised to affine: the gather-and-add
+ * "reduce" of a sharded MSM (NCCL has no elliptic-curve reduction) */
+int b200_g1_sum(b200_ctx* ctx, const uint64_t* xy_mont, const uint8_t* inf, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
+int b200_g2_sum(b200_ctx* ctx, const uint64_t* xy_mont, const uint8_t* inf, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
 int b200_g1_fixed_base(b200_ctx* ctx, const uint64_t* scalars_mont, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
 int b200_g2_fixed_base(b200_ctx* ctx, const uint64_t* scalars_mont, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
 int b200_ntt(b200_ctx* ctx, uint64_t* data_mont, uint32_t log_m, int mode);

@@ -67,6 +67,30 @@ def test_fixed_base_and_group_law(ctx):
         assert oinf[1] == 1 and oinf[4] == 1
 
 
+@pytest.mark.parametrize("group", [1, 2])
+def test_group_sum(ctx, group):
+    """b200_g1_sum / b200_g2_sum (the gather-and-add reduce of a sharded MSM) against the oracle's additions: distinct points,
+    a repeated point (doubling), P + (-P) -> infinity, infinity inputs, the empty sum."""
+    fix, oadd, gsum = (orc.g1_fixed_base, orc.g1_add, ctx.g1_sum) if group == 1 else (orc.g2_fixed_base, orc.g2_add, ctx.g2_sum)
+    w = 8 * group
+    pts, inf = fix(orc.sha512_rng_fr(1 << 48, 9))
+    pts[4] = pts[3]                      # doubling on the way
+    inf[6] = 1
+    want, winf = pts[0].copy(), int(inf[0])
+    for i in range(1, 9):
+        want, winf = oadd(want, winf, pts[i], int(inf[i]))
+    got, ginf = gsum(pts, inf)
+    assert ginf == winf == 0 and np.array_equal(got, np.asarray(want).reshape(-1))
+    # P + (-P): negate y of one point (Fq2: both components)
+    neg = pts[:1].copy()
+    ny = orc.fq_sub(np.zeros((w // 8, 4), np.uint64), neg[0].reshape(-1, 4)[w // 8:])
+    neg[0].reshape(-1, 4)[w // 8:] = ny
+    got, ginf = gsum(np.concatenate([pts[:1], neg]), None)
+    assert ginf == 1
+    got, ginf = gsum(np.zeros((0, w), np.uint64), None)
+    assert ginf == 1
+
+
 @pytest.mark.parametrize("logm", [1, 2, 5, 8, 10, 13, 16])
 def test_ntt_modes(ctx, logm):
     x = orc.sha512_rng_fr(7 * logm, 1 << logm)
@@ -377,6 +401,34 @@ def test_prove_identical_to_oracle(ctx, name, fmt):
             assert np.array_equal(np.asarray(g), np.asarray(e))
         assert key.check_in_exponent(w, got, rs[0], rs[1]) == 0
     pk.free()
+
+
+@pytest.mark.parametrize("name", ["field_1000_1", "binary_1000_10", "field_5000_2"])
+def test_prove_shared_digit_list(ctx, name):
+    """The witness MSMs of one prove (A, B in G2 [and G1 with r,s], L) consuming ONE sorted digit list (msm_shared_prepare /
+    msm_shared_consume) against one sort per query and the oracle; overlapped lanes and serialised; the phase list says which
+    path ran."""
+    circ = CIRCUITS[name]()
+    w = circ.witness()
+    key = orc.Key(circ)
+    pk = _load(ctx, circ, key, orc.FMT_ALT_FULL, eb.FMT_ALT_FULL)
+    rs = orc.sha512_rng_fr(1 << 49, 2)
+    want, want_rs = key.prove(w), key.prove(w, rs[0], rs[1])
+    try:
+        for shared in (1, 0):
+            for overlap in (1, 0):
+                ctx.set_option("shared_sort", shared); ctx.set_option("overlap", overlap)
+                got = pk.prove(w)
+                used = any(nm == "msm.shared_sort" for nm, _ in ctx.timings())
+                assert used == bool(shared and name.startswith("field")), (shared, overlap)    # the 0/1 circuit's queries are too sparse to share
+                for g, e in zip(got, want):
+                    assert np.array_equal(np.asarray(g), np.asarray(e)), (shared, overlap)
+                got = pk.prove(w, rs[0], rs[1])
+                for g, e in zip(got, want_rs):
+                    assert np.array_equal(np.asarray(g), np.asarray(e)), (shared, overlap, "rs")
+    finally:
+        ctx.set_option("shared_sort", 1); ctx.set_option("overlap", 1)
+        pk.free()
 
 
 def test_proof_passes_pairing_verifier(ctx):

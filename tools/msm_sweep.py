@@ -79,7 +79,7 @@ def main():
                 got, inf = bases.msm(device_ptr=s_dev.data_ptr(), n=hi - lo)
                 t = dict(ctx.timings())
                 if world > 1:
-                    # the one exchange step: all ranks' affine partial sums, then <= world - 1 additions
+                    # the one exchange step: all ranks' affine partial sums all-gathered, then added in one kernel
                     part = pin_np
                     part[:limbs] = np.asarray(got).reshape(-1)
                     part[limbs] = int(np.asarray(inf).reshape(-1)[0])
@@ -90,14 +90,7 @@ def main():
                     host = allp.cpu().numpy().view(np.uint64).reshape(world, limbs + 1)
                     pts = np.ascontiguousarray(host[:, :limbs])
                     flg = np.ascontiguousarray(host[:, limbs].astype(np.uint8))
-                    add = ctx.g1_add if group == 1 else ctx.g2_add
-                    while len(pts) > 1:                      # pairwise rounds: log2(world) batched additions
-                        h = len(pts) // 2
-                        a, ai = add(pts[:h], flg[:h], pts[h:2 * h], flg[h:2 * h])
-                        if len(pts) & 1:
-                            a, ai = np.concatenate([a, pts[2 * h:]]), np.concatenate([ai, flg[2 * h:]])
-                        pts, flg = np.ascontiguousarray(a), np.ascontiguousarray(ai)
-                    got, inf = pts[0], flg[:1]
+                    got, inf = (ctx.g1_sum if group == 1 else ctx.g2_sum)(pts, flg)      # one kernel: world - 1 additions
                     got = np.asarray(got).reshape(-1)
                     e1.record()
                     torch.cuda.synchronize()
