@@ -35,7 +35,7 @@ BYTES_PER_G2_POINT = 160
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the accumulate kernel at 2^20 points, from the ncu --set full
 # capture summarised in profiles/r1_ncu_msm_accumulate_2p20_full.csv (window tables: 13 table points are read per scalar,
 # so the traffic is ~12x the canonical 96/160 B per point; HBM stays under 11 % busy)
-NCU_TRAFFIC_BYTES = {("G2", 20): 1.888617e9 + 0.202356e9, ("G1", 20): 1.872888e9 + 0.104280e9}
+NCU_TRAFFIC_BYTES = {("G2", 20): 1.880513e9 + 0.169542e9, ("G1", 20): 1.854417e9 + 0.102273e9}   # profiles/r1_ncu_msm_accumulate_2p20_v2.csv
 
 
 # ----------------------------------------------------------------------------------------------- multi-rank helpers
