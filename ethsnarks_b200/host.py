@@ -105,6 +105,45 @@ class Protoboard:
         return self.cs.num_inputs
 
 
+class Translator:
+    """libsnark::ITranslator (LS/relations/variable.hpp:279-284): maps a master gadget's variable indices to one instance's.
+    `table[i]` is the instance's index of master variable i (table[0] is unused: index 0, the constant ONE, is never
+    translated - `lt.index == 0 ? coeff : assignment[translate(lt.index)] * coeff`, variable.hpp:306-314)."""
+
+    def __init__(self, table):
+        self.table = np.asarray(table, dtype=np.uint32)
+
+    def translate(self, index):
+        return int(self.table[index])
+
+
+def append_constraint_instances(cs, master, translators):
+    """The reference's `r1cs_constraint_light_instance(master_constraint, translator)` (r1cs.hpp:145-211), as its gadgets use
+    it (one instance constraint per master constraint per translator: poseidon.hpp:455-462, sha256_many.hpp:75-82): appends,
+    for every translator in order, all rows of `master` (an R1CS whose variable indices are master-local) with their indices
+    translated, to `cs`.  This is getA/getB/getC (r1cs.hpp:158-185) for all rows at once: one numpy gather per matrix
+    instead of a virtual call and a vector copy per row, and the flattened CSR is what `b200_circuit_load` takes.  The
+    coefficient tables must be the same list (the reference's global ConstantStorage, variable.hpp:47-86)."""
+    assert cs.coeffs == master.coeffs, "master and instances share one coefficient table"
+    out = []
+    for M, N in ((cs.A, master.A), (cs.B, master.B), (cs.C, master.C)):
+        rp, col, ci = (np.asarray(x) for x in M)
+        mrp, mcol, mci = (np.asarray(x) for x in N)
+        nnz = int(mrp[-1])
+        cols, cis, rps = [col], [ci], [rp]
+        base = int(rp[-1])
+        for t in translators:
+            tab = t.table if isinstance(t, Translator) else np.asarray(t, dtype=np.uint32)
+            cols.append(np.where(mcol == 0, np.uint32(0), tab[mcol]).astype(np.uint32))
+            cis.append(mci.astype(np.uint32))
+            rps.append((mrp[1:] + np.uint64(base)).astype(np.uint64))
+            base += nnz
+        out.append((np.concatenate(rps), np.concatenate(cols), np.concatenate(cis)))
+    cs.A, cs.B, cs.C = out
+    cs.num_constraints = len(cs.A[0]) - 1
+    return cs
+
+
 def _csr(rows):
     rp = np.zeros(len(rows) + 1, dtype=np.uint64)
     cols, cis = [], []

@@ -76,3 +76,43 @@ def test_gloo_world2_shard_ranges_cover_and_gather():
                           "127.0.0.1", "--master-port", "29533", script], env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "GLOO_OK" in out.stdout
+
+
+def test_constraint_instances_flatten_like_the_reference():
+    """append_constraint_instances against a per-row restatement of r1cs_constraint_light_instance::getA/B/C and ::evaluateA/B/C
+    (r1cs.hpp:158-200, variable.hpp:306-314): index 0 is never translated, every other index goes through the translator."""
+    import random
+    H = eb.host
+    rng = random.Random(5)
+    # master gadget over local variables 1..4 (0 = ONE): (x1 + 3) * x2 = x3 ; x3 * x3 = x4 + 2*x1
+    coeffs = [1, 3, 2]
+    mA = H._csr([[(1, 0), (0, 1)], [(3, 0)]]); mB = H._csr([[(2, 0)], [(3, 0)]]); mC = H._csr([[(3, 0)], [(4, 0), (1, 2)]])
+    master = H.R1CS(0, 4, mA, mB, mC, coeffs)
+    # host circuit: one plain constraint x1 * x1 = x2, then 3 instances on disjoint variable blocks
+    n_inst, nv = 3, 2 + 4 * 3
+    cs = H.R1CS(1, nv, H._csr([[(1, 0)]]), H._csr([[(1, 0)]]), H._csr([[(2, 0)]]), coeffs)
+    trs = [H.Translator([0] + [3 + 4 * j + i for i in range(4)]) for j in range(n_inst)]
+    H.append_constraint_instances(cs, master, trs)
+    assert cs.num_constraints == 1 + 2 * n_inst
+    # per-row restatement
+    def rows_of(M):
+        rp, col, ci = M
+        return [[(int(col[k]), int(ci[k])) for k in range(int(rp[i]), int(rp[i + 1]))] for i in range(len(rp) - 1)]
+    for name, M, N in (("A", cs.A, mA), ("B", cs.B, mB), ("C", cs.C, mC)):
+        want = rows_of({"A": H._csr([[(1, 0)]]), "B": H._csr([[(1, 0)]]), "C": H._csr([[(2, 0)]])}[name])
+        for t in trs:
+            for r in rows_of(N):
+                want.append([(idx if idx == 0 else t.translate(idx), c) for idx, c in r])
+        assert rows_of(M) == want, name
+    # a satisfying assignment built instance by instance satisfies the flattened system
+    vals = [0] * nv
+    x = rng.randrange(H.R_MOD); vals[0] = x; vals[1] = x * x % H.R_MOD
+    for j in range(n_inst):
+        x1, x2 = rng.randrange(H.R_MOD), rng.randrange(H.R_MOD)
+        x3 = (x1 + 3) * x2 % H.R_MOD
+        x4 = (x3 * x3 - 2 * x1) % H.R_MOD
+        vals[2 + 4 * j: 6 + 4 * j] = [x1, x2, x3, x4]
+    pb = H.Protoboard(cs, vals)
+    assert cs.is_satisfied(pb.values)
+    pb.values[4] = (pb.values[4] + 1) % H.R_MOD
+    assert not cs.is_satisfied(pb.values)

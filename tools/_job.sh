@@ -1,16 +1,14 @@
-python -m pytest tests -m gpu -x -q > gpurun_out/r1_pytest_gpu_final.log 2>&1; echo pytest=$?; tail -3 gpurun_out/r1_pytest_gpu_final.log
-python __graft_entry__.py smoke > gpurun_out/r1_smoke.log 2>&1; echo smoke=$?; tail -2 gpurun_out/r1_smoke.log
-python bench.py --steps 20 --warmup 3 > gpurun_out/r1_bench_prove_2p20.json 2> gpurun_out/x.err; echo bench=$?
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 tools/msm_sweep.py --from 20 --to 26 --g2-max 24 --reps 3 > gpurun_out/r1_msm_sweep_b200_n8.raw 2> gpurun_out/x.err; echo sweep=$?
+grep '^{' gpurun_out/r1_msm_sweep_b200_n8.raw > gpurun_out/r1_msm_sweep_b200_n8.jsonl
+python - <<'P'
+import json
+for l in open('gpurun_out/r1_msm_sweep_b200_n8.jsonl'):
+    d=json.loads(l); print(d['group'], d['log_n'], d['n_gpus'], round(d['ms'],3), round(d['mpoints_per_s'],1), round(d['frac_of_imad_peak'],3), d['in_exponent_ok'], d['phases_ms'].get('msm.exchange'))
+P
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29518 bench.py --gpus 8 --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/r1_bench_prove_2p20_n8.json 2>> gpurun_out/x.err; echo bench8=$?
 python -c "
 import json
-d=json.loads([l for l in open('gpurun_out/r1_bench_prove_2p20.json') if l.startswith('{')][-1])
-print({k:d.get(k) for k in ('metric','value','unit','ms_per_step','e2e','gpu_launches','cpu_baseline','clocks','vs_baseline','dtype','config')}); print(d['roofline']); print(d['phases_ms'])
+d=json.loads([l for l in open('gpurun_out/r1_bench_prove_2p20_n8.json') if l.startswith('{')][-1])
+print({k:d.get(k) for k in ('value','ms_per_step','n_gpus','e2e','sharded')})
 "
-python bench.py --log-m 24 --steps 5 --warmup 3 --no-cpu-baseline --mode replicas > gpurun_out/r1_bench_prove_2p24.json 2>> gpurun_out/x.err; echo rc24=$?
-python -c "
-import json
-d=json.loads([l for l in open('gpurun_out/r1_bench_prove_2p24.json') if l.startswith('{')][-1])
-print({k:d.get(k) for k in ('value','ms_per_step','e2e')}); print(d.get('phases_ms'))
-"
-python tools/timeline.py > gpurun_out/r1_timeline_prove_2p20.txt 2>>gpurun_out/x.err; head -40 gpurun_out/r1_timeline_prove_2p20.txt
 tail -3 gpurun_out/x.err
