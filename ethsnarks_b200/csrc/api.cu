@@ -222,6 +222,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "g2_pair")) ctx->g2_pair = (int)value;
     else if (!strcmp(name, "ntt_radix4")) ctx->ntt_radix4 = (int)value;
     else if (!strcmp(name, "shared_sort")) ctx->shared_sort = (int)value;
+    else if (!strcmp(name, "pair_reduce")) ctx->pair_reduce = (int)value;
     else if (!strcmp(name, "reduce_fold")) ctx->reduce_fold = (int)value;
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
     else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;

@@ -103,6 +103,60 @@ static B200_DEV void pair_add_mixed(const PairLane<MODE>& ln, HalfXYZZ& a, const
     a.ZZZ = ln.mul(a.ZZZ, zzzo, PPP, PPPo);
 }
 
+// 2 * a for a general XYZZ point (dbl-2008-s-1); rare: only when two partial sums of one bucket coincide
+template <int MODE>
+static __device__ __noinline__ HalfXYZZ pair_dbl(PairLane<MODE> ln, HalfXYZZ a) {
+    const Fq U = a.Y.dbl(), Uo = ln.other(U);
+    if (U.is_zero() && Uo.is_zero()) return ln.inf();
+    const Fq V = ln.sqr(U, Uo), Vo = ln.other(V);
+    const Fq W = ln.mul(U, Uo, V, Vo), Wo = ln.other(W);
+    const Fq S = ln.mul(a.X, ln.other(a.X), V, Vo);
+    const Fq xx = ln.sqr(a.X, ln.other(a.X));
+    const Fq M = xx.dbl() + xx, Mo = ln.other(M);
+    HalfXYZZ r;
+    r.X = ln.sqr(M, Mo) - S.dbl();
+    const Fq D = S - r.X;
+    r.Y = ln.mul(M, Mo, D, ln.other(D)) - ln.mul(W, Wo, a.Y, ln.other(a.Y));
+    r.ZZ = ln.mul(V, Vo, a.ZZ, ln.other(a.ZZ));
+    r.ZZZ = ln.mul(W, Wo, a.ZZZ, ln.other(a.ZZZ));
+    return r;
+}
+
+// a += b, both XYZZ   (add-2008-s: 12M + 2S in Fq2), complete; every branch condition is the same in both lanes of the pair.
+// The one-thread form (XYZZ<Fq2>::add) needs 174-184 registers in the reduction kernels: 1.9 warps per scheduler and the IMAD
+// pipe 45-57 % busy (profiles/r1_ncu_other_kernels.txt).
+template <int MODE>
+static B200_DEV void pair_add_full(const PairLane<MODE>& ln, HalfXYZZ& a, const HalfXYZZ& b) {
+    const Fq bzo = ln.other(b.ZZ);
+    if (b.ZZ.is_zero() && bzo.is_zero()) return;
+    const Fq azo = ln.other(a.ZZ);
+    if (a.ZZ.is_zero() && azo.is_zero()) { a = b; return; }
+    const Fq azzzo = ln.other(a.ZZZ), bzzzo = ln.other(b.ZZZ);
+    const Fq U1 = ln.mul(a.X, ln.other(a.X), b.ZZ, bzo), U2 = ln.mul(b.X, ln.other(b.X), a.ZZ, azo);
+    const Fq S1 = ln.mul(a.Y, ln.other(a.Y), b.ZZZ, bzzzo), S2 = ln.mul(b.Y, ln.other(b.Y), a.ZZZ, azzzo);
+    const Fq Pp = U2 - U1, R = S2 - S1;
+    const Fq Ppo = ln.other(Pp), Ro = ln.other(R);
+    if (Pp.is_zero() && Ppo.is_zero()) {
+        if (R.is_zero() && Ro.is_zero()) a = pair_dbl(ln, a); else a = ln.inf();
+        return;
+    }
+    const Fq PP = ln.sqr(Pp, Ppo), PPo = ln.other(PP);
+    const Fq PPP = ln.mul(Pp, Ppo, PP, PPo), PPPo = ln.other(PPP);
+    const Fq Q = ln.mul(U1, ln.other(U1), PP, PPo);
+    const Fq X3 = ln.sqr(R, Ro) - PPP - Q.dbl();
+    const Fq D = Q - X3;
+    a.Y = ln.mul(R, Ro, D, ln.other(D)) - ln.mul(S1, ln.other(S1), PPP, PPPo);
+    a.X = X3;
+    const Fq Z2 = ln.mul(a.ZZ, azo, b.ZZ, bzo);
+    a.ZZ = ln.mul(Z2, ln.other(Z2), PP, PPo);
+    const Fq Z3 = ln.mul(a.ZZZ, azzzo, b.ZZZ, bzzzo);
+    a.ZZZ = ln.mul(Z3, ln.other(Z3), PPP, PPPo);
+}
+
+static B200_DEV HalfXYZZ pair_load(const G2XYZZ* src, bool imag) {
+    const Fq* f = (const Fq*)src + (imag ? 1 : 0);      // X.a X.b Y.a Y.b ZZ.a ZZ.b ZZZ.a ZZZ.b
+    return HalfXYZZ{f[0], f[2], f[4], f[6]};
+}
 static B200_DEV void pair_store(G2XYZZ* dst, bool imag, const HalfXYZZ& a) {
     Fq* f = (Fq*)dst + (imag ? 1 : 0);      // X.a X.b Y.a Y.b ZZ.a ZZ.b ZZZ.a ZZZ.b
     f[0] = a.X; f[2] = a.Y; f[4] = a.ZZ; f[6] = a.ZZZ;

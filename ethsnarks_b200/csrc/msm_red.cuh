@@ -1,6 +1,7 @@
 #pragma once
 // Stages 5 and 6 of the MSM (msm_common.cuh): stitching chunk partial sums into buckets, and the bucket reductions.
 #include "msm_common.cuh"
+#include "msm_acc_pair.cuh"
 
 namespace b200 {
 
@@ -168,6 +169,69 @@ __global__ void __launch_bounds__(128) msm_rc_partial(const typename G::Pt* __re
     for (uint32_t k = 1; k < Kr; ++k) acc.add(src[k]);
     pr[(size_t)blockIdx.y * nrow + id] = acc;
 }
+// Stage A for G2 with one output per LANE PAIR (msm_acc_pair.cuh: pair_add_full); same outputs as msm_rc_partial<G2T>.
+template <typename G>
+__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_rc_partial_pair(const G2XYZZ* __restrict__ buckets, uint32_t half, uint32_t s, uint32_t K,
+                                                                          G2XYZZ* __restrict__ pc, G2XYZZ* __restrict__ pr) {
+    const uint32_t S = 1u << s, Rn = half >> s;
+    const uint32_t Kc = min(K, Rn), Kr = min(K, S);
+    const uint32_t ncol = (Rn / Kc) * S, nrow = Rn * (S / Kr);
+    const G2XYZZ* B = buckets + (size_t)blockIdx.y * half;
+    const uint32_t gt = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t id = gt >> 1;
+    PairLane<2> ln;
+    ln.imag = gt & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    if (id < ncol) {
+        const uint32_t g = id >> s, lo = id & (S - 1);
+        const G2XYZZ* src = B + (size_t)g * Kc * S + lo;
+        HalfXYZZ acc = pair_load(src, ln.imag);
+        for (uint32_t k = 1; k < Kc; ++k) pair_add_full(ln, acc, pair_load(src + (size_t)k * S, ln.imag));
+        pair_store(&pc[(size_t)blockIdx.y * ncol + id], ln.imag, acc);
+        return;
+    }
+    id -= ncol;
+    if (id >= nrow) return;
+    const G2XYZZ* src = B + (size_t)id * Kr;
+    HalfXYZZ acc = pair_load(src, ln.imag);
+    for (uint32_t k = 1; k < Kr; ++k) pair_add_full(ln, acc, pair_load(src + k, ln.imag));
+    pair_store(&pr[(size_t)blockIdx.y * nrow + id], ln.imag, acc);
+}
+// msm_finalize_chunks for G2 with one chunk edge per lane pair
+template <typename G>
+__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_finalize_chunks_pair(const uint32_t* __restrict__ keys, const uint64_t* __restrict__ offsets,
+                                                                               uint32_t nb, uint32_t L, G2XYZZ* __restrict__ buckets,
+                                                                               const G2XYZZ* __restrict__ pfirst, const G2XYZZ* __restrict__ plast,
+                                                                               uint32_t* __restrict__ big_count, uint32_t* __restrict__ big_list) {
+    const uint64_t gt = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t id = gt >> 1;
+    PairLane<2> ln;
+    ln.imag = gt & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    const uint64_t M = offsets[nb];
+    if (id < nb) {
+        const uint64_t s = offsets[id], e = offsets[id + 1];
+        if (s == e) pair_store(&buckets[id], ln.imag, ln.inf());
+        else {
+            const uint64_t t0 = s / L, t1 = (e - 1) / L;
+            if (t0 == t1) {
+                if (s == t0 * L) pair_store(&buckets[id], ln.imag, pair_load(&pfirst[t0], ln.imag));
+                else if (e == min((t0 + 1) * (uint64_t)L, M)) pair_store(&buckets[id], ln.imag, pair_load(&plast[t0], ln.imag));
+            }
+        }
+    }
+    const uint64_t pos = id * L;
+    if (id == 0 || pos >= M) return;
+    const uint32_t b = keys[pos];
+    const uint64_t s = offsets[b];
+    if (s >= pos || s / L != id - 1) return;
+    const uint64_t t0 = id - 1, t1 = (offsets[b + 1] - 1) / L;
+    if (t1 - t0 > B200_BIG_SPAN) { if (!ln.imag) big_list[atomicAdd(big_count, 1u)] = b; return; }
+    HalfXYZZ acc = pair_load((s == t0 * L) ? &pfirst[t0] : &plast[t0], ln.imag);
+    for (uint64_t t = id; t <= t1; ++t) pair_add_full(ln, acc, pair_load(&pfirst[t], ln.imag));
+    pair_store(&buckets[b], ln.imag, acc);
+}
+
 // Warp-level tree sum of one point per lane; the result is in lane 0.  The stages below run one warp per output so that
 // no resident warp sits idle at a block barrier holding 255 registers per thread.
 template <typename Pt>
@@ -229,6 +293,32 @@ __global__ void __launch_bounds__(128) msm_rc_fold(typename G::Pt* __restrict__ 
     Pt a = src[lg];
     a.add(src[lg + (1u << rwl)]);
     if (rwl == 0) V[(size_t)blockIdx.y * (S + Rn) + S + hi] = a; else src[lg] = a;
+}
+// msm_rc_fold for G2 with one addition per lane pair (half the latency of the one-thread addition per pass)
+template <typename G>
+__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_rc_fold_pair(G2XYZZ* __restrict__ pc, uint32_t ncol, uint32_t colcur, G2XYZZ* __restrict__ pr,
+                                                                       uint32_t nrow, uint32_t rw0, uint32_t rwl, uint32_t rows_active, uint32_t S,
+                                                                       uint32_t Rn, G2XYZZ* __restrict__ V) {
+    const uint32_t gt = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t id = gt >> 1;
+    PairLane<2> ln;
+    ln.imag = gt & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    const uint32_t nc2 = colcur > S ? colcur >> 1 : 0;
+    if (id < nc2) {
+        G2XYZZ* src = pc + (size_t)blockIdx.y * ncol;
+        HalfXYZZ a = pair_load(&src[id], ln.imag);
+        pair_add_full(ln, a, pair_load(&src[id + nc2], ln.imag));
+        pair_store(nc2 == S ? &V[(size_t)blockIdx.y * (S + Rn) + id] : &src[id], ln.imag, a);
+        return;
+    }
+    id -= nc2;
+    if (!rows_active || id >= (Rn << rwl)) return;
+    const uint32_t hi = id >> rwl, lg = id & ((1u << rwl) - 1);
+    G2XYZZ* src = pr + (size_t)blockIdx.y * nrow + (size_t)hi * rw0;
+    HalfXYZZ a = pair_load(&src[lg], ln.imag);
+    pair_add_full(ln, a, pair_load(&src[lg + (1u << rwl)], ln.imag));
+    pair_store(rwl == 0 ? &V[(size_t)blockIdx.y * (S + Rn) + S + hi] : &src[lg], ln.imag, a);
 }
 // Stage C: one warp per (weight bit i, slice of B200_RC_SLICE entries of V): sum of the selected C_lo and R_hi.
 #define B200_RC_SLICE 128
@@ -298,7 +388,15 @@ void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uin
     B200_CUDA_CHECK(cudaMemsetAsync(big, 0, 4, st));
     if (ctx->finalize_chunks) {
         const uint64_t threads = std::max<uint64_t>(p.nb, p.nchunks);
-        msm_finalize_chunks<G><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(keys, offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+        if constexpr (sizeof(Pt) > 128) {
+            if (ctx->pair_reduce)
+                msm_finalize_chunks_pair<G><<<(unsigned)((2 * threads + 127) / 128), 128, 0, st>>>(
+                    keys, offsets, p.nb, p.L, (G2XYZZ*)buckets, (const G2XYZZ*)pfirst, (const G2XYZZ*)plast, big, big + 1);
+            else
+                msm_finalize_chunks<G><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(keys, offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+        } else {
+            msm_finalize_chunks<G><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(keys, offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
+        }
     } else {
         msm_finalize<G><<<(p.nb + 127) / 128, 128, 0, st>>>(offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
     }
@@ -326,7 +424,12 @@ void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void*
         Pt* U = (Pt*)ctx->scratch("msm_rc_u", (size_t)Wr * nbits * sizeof(Pt));
         const uint32_t nslice = (S + Rn + B200_RC_SLICE - 1) / B200_RC_SLICE;
         Pt* Us = (Pt*)ctx->scratch("msm_rc_us", (size_t)Wr * nbits * nslice * sizeof(Pt));
-        msm_rc_partial<G><<<dim3((ncol + nrow + 127) / 128, Wr), 128, 0, st>>>(B, p.half, s, K, pc, pr);
+        bool pair_a = false;
+        if constexpr (sizeof(Pt) > 128) pair_a = ctx->pair_reduce != 0;
+        if constexpr (sizeof(Pt) > 128) {
+            if (pair_a) msm_rc_partial_pair<G><<<dim3((2 * (ncol + nrow) + 127) / 128, Wr), 128, 0, st>>>((const G2XYZZ*)B, p.half, s, K, (G2XYZZ*)pc, (G2XYZZ*)pr);
+        }
+        if (!pair_a) msm_rc_partial<G><<<dim3((ncol + nrow + 127) / 128, Wr), 128, 0, st>>>(B, p.half, s, K, pc, pr);
         if ((ctx->reduce_fold == 2 || (ctx->reduce_fold == 1 && p.half >= (1u << 17))) && Rn / Kc >= 2 && S / Kr >= 2) {
             uint32_t colcur = ncol, rw = S / Kr;
             while (colcur > S || rw > 1) {
@@ -334,7 +437,13 @@ void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void*
                 uint32_t rwl = 0;
                 while (rw > 1 && (2u << rwl) < rw) ++rwl;          // log2(rw / 2)
                 const uint32_t nr2 = rw > 1 ? Rn << rwl : 0;
-                msm_rc_fold<G><<<dim3((nc2 + nr2 + 127) / 128, Wr), 128, 0, st>>>(pc, ncol, colcur, pr, nrow, S / Kr, rwl, rw > 1, S, Rn, V);
+                bool pair_f = false;
+                if constexpr (sizeof(Pt) > 128) {
+                    pair_f = ctx->pair_reduce != 0;
+                    if (pair_f) msm_rc_fold_pair<G><<<dim3((2 * (nc2 + nr2) + 127) / 128, Wr), 128, 0, st>>>(
+                                    (G2XYZZ*)pc, ncol, colcur, (G2XYZZ*)pr, nrow, S / Kr, rwl, rw > 1, S, Rn, (G2XYZZ*)V);
+                }
+                if (!pair_f) msm_rc_fold<G><<<dim3((nc2 + nr2 + 127) / 128, Wr), 128, 0, st>>>(pc, ncol, colcur, pr, nrow, S / Kr, rwl, rw > 1, S, Rn, V);
                 ctx->launches++;
                 if (colcur > S) colcur /= 2;
                 if (rw > 1) rw /= 2;

@@ -71,6 +71,7 @@ unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by 
  *                     3 = lazy + out-of-line products, 0 = one thread per point
  *   "finalize_chunks" 1 = stitch chunk partial sums with one thread per chunk edge (default), 0 = one per bucket
  *   "reduce_fold"     stage B of the bucket reduction as halving passes: 1 = for >= 2^17 buckets (default), 2 = always, 0 = never
+ *   "pair_reduce"     1 = G2 finalize and bucket-reduction additions with one full addition per lane pair (default), 0 = per thread
  *   "reduce_1d"       1 = running-sum bucket reduction instead of the two-dimensional one
  *   "ntt_radix4"      1 = NTT passes with two stages per shared-memory round trip (default), 0 = one
  *   "shared_sort"     1 = the witness MSMs of one prove consume ONE sorted digit list when their queries are dense (default)

@@ -135,6 +135,7 @@ def test_ntt_large_roundtrip_and_linearity(ctx):
 
 NTT_RADIX4_DEFAULT = 1
 REDUCE_FOLD_DEFAULT = 1
+PAIR_REDUCE_DEFAULT = 1
 
 
 def _scalar_mix(n, seed, kind):
@@ -331,6 +332,36 @@ def test_msm_finalize_per_chunk_edge(ctx, group):
         ctx.set_option("finalize_chunks", 1); ctx.set_option("window", 0)
         ctx.set_option("chunk", 0); ctx.set_option("g2_pair", 2)
         plain.free(); tabled.free()
+
+
+def test_msm_g2_lane_pair_full_addition(ctx):
+    """pair_add_full / pair_dbl (msm_finalize_chunks_pair, msm_rc_partial_pair: one FULL Fq2 addition per lane pair) against the
+    one-thread kernels and the oracle.  Chunks of 1-3 pairs push every special case into the finalize additions: equal
+    partial sums (doubling), opposite ones (infinity), infinity operands; binary scalars give buckets for the block tree."""
+    n = 2000
+    bases, inf = orc.g2_fixed_base(orc.sha512_rng_fr(1 << 50, n))
+    s = _scalar_mix(n, 79, "dense")
+    bases[1::2][:300] = bases[0::2][:300]; s[1::2][:300] = s[0::2][:300]                   # P, P in one bucket
+    s[601:1000:2] = orc.fr_sub(np.zeros((200, 4), np.uint64), s[600:1000:2])            # k P + (-k) P
+    bases[601:1000:2] = bases[600:1000:2]
+    inf[1100:1130] = 1
+    s[1400:2000] = _scalar_mix(600, 80, "binary")
+    want, winf = orc.msm_g2(bases, inf, s)
+    tabled = eb.Bases(ctx, 2, xy=bases, inf=inf)
+    try:
+        for window, chunk in ((11, 1), (12, 2), (0, 3), (14, 0)):
+            if window:
+                tabled.precompute(window)
+            for pr in (1, 0):
+                ctx.set_option("pair_reduce", pr); ctx.set_option("chunk", chunk); ctx.set_option("window", window)
+                got, ginf = ctx.msm_g2(bases, inf, s)
+                assert ginf == winf and np.array_equal(got, want), (window, chunk, pr, "plain")
+                if window:
+                    got, ginf = tabled.msm(s)
+                    assert ginf == winf and np.array_equal(got, want), (window, chunk, pr, "tables")
+    finally:
+        ctx.set_option("pair_reduce", PAIR_REDUCE_DEFAULT); ctx.set_option("chunk", 0); ctx.set_option("window", 0)
+        tabled.free()
 
 
 def test_msm_large_in_the_exponent(ctx):
