@@ -169,9 +169,12 @@ __global__ void __launch_bounds__(128) msm_rc_partial(const typename G::Pt* __re
     for (uint32_t k = 1; k < Kr; ++k) acc.add(src[k]);
     pr[(size_t)blockIdx.y * nrow + id] = acc;
 }
+#ifndef B200_G2_PAIR_RED_MINB
+#define B200_G2_PAIR_RED_MINB 3     // resident blocks per SM the lane-pair full-addition kernels are compiled for
+#endif
 // Stage A for G2 with one output per LANE PAIR (msm_acc_pair.cuh: pair_add_full); same outputs as msm_rc_partial<G2T>.
 template <typename G>
-__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_rc_partial_pair(const G2XYZZ* __restrict__ buckets, uint32_t half, uint32_t s, uint32_t K,
+__global__ void __launch_bounds__(128, B200_G2_PAIR_RED_MINB) msm_rc_partial_pair(const G2XYZZ* __restrict__ buckets, uint32_t half, uint32_t s, uint32_t K,
                                                                           G2XYZZ* __restrict__ pc, G2XYZZ* __restrict__ pr) {
     const uint32_t S = 1u << s, Rn = half >> s;
     const uint32_t Kc = min(K, Rn), Kr = min(K, S);
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_rc_partial_pair(co
 }
 // msm_finalize_chunks for G2 with one chunk edge per lane pair
 template <typename G>
-__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_finalize_chunks_pair(const uint32_t* __restrict__ keys, const uint64_t* __restrict__ offsets,
+__global__ void __launch_bounds__(128, B200_G2_PAIR_RED_MINB) msm_finalize_chunks_pair(const uint32_t* __restrict__ keys, const uint64_t* __restrict__ offsets,
                                                                                uint32_t nb, uint32_t L, G2XYZZ* __restrict__ buckets,
                                                                                const G2XYZZ* __restrict__ pfirst, const G2XYZZ* __restrict__ plast,
                                                                                uint32_t* __restrict__ big_count, uint32_t* __restrict__ big_list) {
@@ -296,7 +299,7 @@ __global__ void __launch_bounds__(128) msm_rc_fold(typename G::Pt* __restrict__ 
 }
 // msm_rc_fold for G2 with one addition per lane pair (half the latency of the one-thread addition per pass)
 template <typename G>
-__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_rc_fold_pair(G2XYZZ* __restrict__ pc, uint32_t ncol, uint32_t colcur, G2XYZZ* __restrict__ pr,
+__global__ void __launch_bounds__(128, B200_G2_PAIR_RED_MINB) msm_rc_fold_pair(G2XYZZ* __restrict__ pc, uint32_t ncol, uint32_t colcur, G2XYZZ* __restrict__ pr,
                                                                        uint32_t nrow, uint32_t rw0, uint32_t rwl, uint32_t rows_active, uint32_t S,
                                                                        uint32_t Rn, G2XYZZ* __restrict__ V) {
     const uint32_t gt = blockIdx.x * blockDim.x + threadIdx.x;
