@@ -28,7 +28,7 @@ SYMBOLS = [
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
     "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
-    "b200_generate_key", "b200_g1_sum", "b200_g2_sum",
+    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc",
 ]
 
 
@@ -175,6 +175,11 @@ class Context:
 
     def g2_sum(self, xy, inf=None):
         return self._gsum(self.lib.b200_g2_sum, 16, xy, inf)
+
+    def g1_sum_noalloc(self, d_xy_ptr, n, d_out_ptr):
+        """b200_g1_sum_noalloc: DEVICE pointers in and out (n x 8 limbs in; 8 limbs + u32 flag out), queued on the context's
+        stream without synchronising; allocates nothing (static device scratch)."""
+        self.check(self.lib.b200_g1_sum_noalloc(self.h, C.c_void_p(d_xy_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr)), "g1_sum_noalloc")
 
     def _fixed(self, fn, w, scalars):
         s = _arr(scalars)

@@ -95,6 +95,18 @@ int b200_g2_add(b200_ctx* ctx, const uint64_t* a_xy, const uint8_t* a_inf, const
  * "reduce" of a sharded MSM (NCCL has no elliptic-curve reduction) */
 int b200_g1_sum(b200_ctx* ctx, const uint64_t* xy_mont, const uint8_t* inf, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
 int b200_g2_sum(b200_ctx* ctx, const uint64_t* xy_mont, const uint8_t* inf, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
+/* b200_g1_sum for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * No counterpart in the reference.  The call allocates nothing — no cudaMalloc,
+ * cudaFree or allocating library routine: its working memory (one partial sum per block of the first of its two kernels) is a
+ * file-scope 32 KB __device__ array that every GPU loading the library holds until exit.  d_xy_mont and d_out are DEVICE
+ * pointers of the caller: n affine points (8 limbs each, Montgomery, (0,0) = infinity) in; the affine sum (8 limbs,
+ * Montgomery, (0,0) at infinity) followed by a uint32 infinity flag out, i.e. 68 bytes.  The two kernels are queued on
+ * b200_stream(ctx) and the call returns without synchronising.  n > B200_G1_SUM_NOALLOC_MAX is rejected with B200_ERR_ARG
+ * (text in b200_last_error).  All calls on one device share the array and it keeps the last call's contents (nothing in it
+ * needs clearing: every slot that is read was written by the same call); calls that overlap on the GPU race on it.  The first
+ * call on a device looks the array's address up (cudaGetSymbolAddress) — make it once before starting a graph capture. */
+#define B200_G1_SUM_NOALLOC_MAX (1u << 20)
+int b200_g1_sum_noalloc(b200_ctx* ctx, const uint64_t* d_xy_mont, size_t n, uint64_t* d_out);
 int b200_g1_fixed_base(b200_ctx* ctx, const uint64_t* scalars_mont, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
 int b200_g2_fixed_base(b200_ctx* ctx, const uint64_t* scalars_mont, size_t n, uint64_t* out_xy_mont, uint8_t* out_inf);
 int b200_ntt(b200_ctx* ctx, uint64_t* data_mont, uint32_t log_m, int mode);
