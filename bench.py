@@ -146,12 +146,12 @@ def verify_in_the_exponent(eb, ctx, key, witness, proof, dims):
 
 
 # ----------------------------------------------------------------------------------------------- workload
-def build_workload(eb, ctx, log_m, rank, world):
+def build_workload(eb, ctx, log_m, rank, world, flavour="field"):
     """Synthetic R1CS (reference generator) + a device-resident synthetic key of the same shape, sliced per rank."""
     m = 1 << log_m
     ni = 1
     nc = m - ni - 1
-    pb = eb.generate_r1cs_example_with_field_input(nc, ni)
+    pb = eb.generate_r1cs_example_with_binary_input(nc, ni) if flavour == "binary" else eb.generate_r1cs_example_with_field_input(nc, ni)
     cs = pb.cs
     nv = cs.num_variables
     witness = eb.host.fr_to_mont(pb.values)
@@ -176,65 +176,89 @@ def build_workload(eb, ctx, log_m, rank, world):
 
 
 # ----------------------------------------------------------------------------------------------- CPU arm
-def cpu_prove_sample(sample_log_m, steps, warmup, target_log_m=None):
-    """Times the CPU implementation of the path on the host cores, key generation excluded.
-    If oracle/_ref/ref_prove exists (the reference's own prover templates built from /root/reference by
-    oracle/ref/Makefile) it is the thing timed (kind "reference", all OpenMP threads); otherwise the oracle port
-    (kind "port").  Returns (seconds per prove extrapolated to 2^target_log_m, threads, kind, description)."""
+def host_cpu():
+    """(model name, logical cores) of the host the CPU arm runs on"""
+    model = "unknown"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return model, os.cpu_count() or 1
+
+
+def cpu_prove(log_m, steps, warmup, budget_s, flavour="field"):
+    """Times the CPU implementation of the path on the host cores ON THE BENCHMARK'S OWN INSTANCE (the 2^log_m-constraint
+    R1CS, no extrapolation), key generation and key parsing excluded: every step is one whole prove, the scope of the
+    reference's "Call to r1cs_gg_ppzksnark_zok_prover" block (...zok.tcc:454-544).
+    If oracle/_ref/ref_prove exists (the reference's own prover templates built from /root/reference by oracle/ref/Makefile,
+    alt_bn128 build) it is the thing timed (kind "reference"); otherwise the oracle port (kind "port").  All host threads
+    are used: OMP_NUM_THREADS is set explicitly, because torchrun exports OMP_NUM_THREADS=1 to its workers.
+    The run is bounded: if warmup + steps proves would take longer than budget_s, the warm-up is cut to one prove and the
+    timed proves to what fits (never fewer than 5, or `steps` if smaller); the counts actually run are returned.
+    Returns dict(times=[seconds per timed prove], warmup=.., threads=.., kind=.., cpu=.., desc=..)."""
+    model, cores = host_cpu()
+    os.environ["OMP_NUM_THREADS"] = str(cores)        # before liboracle (OpenMP) is loaded: the oracle generates the key
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import orc
     import orc_ref
-    target_log_m = target_log_m or sample_log_m
     use_ref = orc_ref.available()
-    threads = int(orc.lib().orc_num_threads())
-
-    def one(log_m):
-        m = 1 << log_m
-        circ = orc.Circuit.synth_field(m - 2, 1)
-        w = circ.witness()
-        key = orc.Key(circ)
-        if use_ref:
-            return orc_ref.prove(circ, w, key, repeats=warmup + steps)[2]   # best of the repeats, timed inside the binary
-        ts = []
+    m = 1 << log_m
+    circ = orc.Circuit.synth_binary(m - 2, 1) if flavour == "binary" else orc.Circuit.synth_field(m - 2, 1)
+    w = circ.witness()
+    key = orc.Key(circ)
+    floor = min(steps, 5)
+    if use_ref:
+        all_t = orc_ref.prove(circ, w, key, repeats=warmup + steps, threads=cores, all_times=True, budget_s=budget_s,
+                              min_repeats=min(warmup, 1) + floor)[2]
+    else:
+        all_t, used = [], 0.0
         for i in range(warmup + steps):
             t0 = time.perf_counter()
             key.prove(w)
-            if i >= warmup:
-                ts.append(time.perf_counter() - t0)
-        return float(np.mean(ts))
-
-    t_hi = one(sample_log_m)
-    if target_log_m == sample_log_m:
-        return t_hi, threads, "reference" if use_ref else "port", "2^%d-constraint instance, measured directly" % sample_log_m
-    # two-point fit T(m) = a + b m: the reference pays a fixed 2 * 2^16 bucket additions per window whatever the size
-    lo = max(10, sample_log_m - 2)
-    t_lo = one(lo)
-    b_ = (t_hi - t_lo) / ((1 << sample_log_m) - (1 << lo))
-    a_ = t_hi - b_ * (1 << sample_log_m)
-    sec = max(a_, 0.0) + b_ * (1 << target_log_m)
-    desc = ("proves of 2^%d- (%.2f s) and 2^%d-constraint (%.2f s) instances of the same R1CS on the host cores, "
-            "extrapolated T = a + b*m to 2^%d" % (lo, t_lo, sample_log_m, t_hi, target_log_m))
-    return sec, threads, "reference" if use_ref else "port", desc
+            all_t.append(time.perf_counter() - t0)
+            used += all_t[-1]
+            if used > budget_s and i + 1 >= min(warmup, 1) + floor:
+                break
+    wu = warmup if len(all_t) == warmup + steps else min(warmup, 1)
+    times = all_t[wu:]
+    kind = "reference" if use_ref else "port"
+    desc = ("%d whole proves of the 2^%d-constraint %s instance itself (no extrapolation) after %d warm-up, %s, %d OpenMP threads on %s; "
+            "the reference MSM uses at most 16 threads (one per window, multiexp.tcc:534-541)" %
+            (len(times), log_m, "0/1-witness" if flavour == "binary" else "synthetic", wu,
+             "oracle/_ref/ref_prove = the reference's own prover templates, alt_bn128 build (not the reference's default mcl curve code), -O3 -march=x86-64-v3"
+             if use_ref else "oracle port", cores, model))
+    return dict(times=times, warmup=wu, threads=cores, kind=kind, cpu=model, desc=desc)
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample_log = min(args.log_m, args.cpu_sample_log_m)
-    sec, cores, kind, sample = cpu_prove_sample(sample_log, args.steps, args.warmup, args.log_m)
-    scale = 1
-    value = 1.0 / sec
+    r = cpu_prove(args.log_m, args.steps, args.warmup, args.cpu_budget_s, args.flavour)
+    times = r["times"]
+    mean_s, med_s = float(np.mean(times)), float(np.median(times))
+    value = 1.0 / mean_s
     line = {
         "impl": "reference", "metric": "groth16_proofs_per_sec", "value": value, "unit": "proofs/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * scale * 1e3, "higher_is_better": True, "scaling": "strong",
+        "steps": len(times), "warmup": r["warmup"], "ms_per_step": mean_s * 1e3, "median_ms_per_step": med_s * 1e3,
+        "min_ms_per_step": float(np.min(times)) * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery)", "data": "synthetic",
-        "config": {"workload": "synthetic R1CS 2^%d constraints, full prove (4 MSMs + H NTT chain)" % args.log_m, "log_m": args.log_m},
-        "cpu_baseline": {"value": value, "unit": "proofs/s", "cores": cores, "kind": kind, "sample": sample},
+        "config": workload_config(args.log_m, args.flavour),
+        "cpu_baseline": {"value": value, "unit": "proofs/s", "cores": r["threads"], "kind": r["kind"], "sample": r["desc"], "cpu": r["cpu"]},
         "e2e": {"value": value, "unit": "proofs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+def workload_config(log_m, flavour):
+    if flavour == "binary":
+        return {"workload": "0/1-witness R1CS 2^%d constraints (generate_r1cs_example_with_binary_input), full prove (4 MSMs + H NTT chain)" % log_m,
+                "log_m": log_m}
+    return {"workload": "synthetic R1CS 2^%d constraints, full prove (4 MSMs + H NTT chain)" % log_m, "log_m": log_m}
 
 
 # ----------------------------------------------------------------------------------------------- GPU arm
@@ -284,7 +308,7 @@ def run_ours(args):
     # sharded 1/N per GPU (the north-star's MSM split; strong scaling, it shortens the latency of ONE proof)
     sharded = None
     if world > 1 and args.mode == "both":
-        skey, switness, sdims = build_workload(eb, ctx, args.log_m, rank, world)
+        skey, switness, sdims = build_workload(eb, ctx, args.log_m, rank, world, args.flavour)
         sw_dev = torch.from_numpy(switness.view(np.int64)).to(dev)
 
         def sstep():
@@ -306,7 +330,7 @@ def run_ours(args):
         del skey, sw_dev
         torch.cuda.synchronize()
 
-    key, witness, dims = build_workload(eb, ctx, args.log_m, rank if shard else 0, world if shard else 1)
+    key, witness, dims = build_workload(eb, ctx, args.log_m, rank if shard else 0, world if shard else 1, args.flavour)
     nbytes_w = witness.nbytes
     w_dev = torch.from_numpy(witness.view(np.int64)).to(dev)            # resident witness (`value`)
     w_pin = torch.from_numpy(witness.view(np.int64)).pin_memory()       # pinned host witness (`e2e`)
@@ -452,8 +476,7 @@ def run_ours(args):
         "metric": "groth16_proofs_per_sec", "value": value, "unit": "proofs/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "strong" if shard else "weak", "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery)", "data": "synthetic",
-        "config": {"workload": "synthetic R1CS 2^%d constraints, full prove (4 MSMs + H NTT chain)" % args.log_m, "log_m": args.log_m,
-                   "num_inputs": dims["ni"], "msm_lengths": {"A": dims["nA"], "B_g2": dims["nB"], "H": dims["nH"], "L": dims["nL"]},
+        "config": {**workload_config(args.log_m, args.flavour), "num_inputs": dims["ni"], "msm_lengths": {"A": dims["nA"], "B_g2": dims["nB"], "H": dims["nH"], "L": dims["nL"]},
                    "parallelism": ("key sharded 1/%d per GPU, partial sums all-gathered" % world) if shard else
                                   (("%d independent replicas" % world if world > 1 else "single GPU") +
                                    (", %d proofs in flight per GPU on one resident key" % len(slots) if len(slots) > 1 else "")),
@@ -469,9 +492,9 @@ def run_ours(args):
     if sharded:
         line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
-        sample_log = min(args.log_m, args.cpu_sample_log_m)
-        sec, cores, kind, desc = cpu_prove_sample(sample_log, 1, 0, args.log_m)
-        line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "proofs/s", "cores": cores, "kind": kind, "sample": desc}
+        r = cpu_prove(args.log_m, 3, 1, 30.0, args.flavour)        # bounded: 1 warm-up + 3 timed whole proves of this instance
+        line["cpu_baseline"] = {"value": 1.0 / float(np.median(r["times"])), "unit": "proofs/s", "cores": r["threads"], "kind": r["kind"],
+                                "sample": r["desc"] + "; value = 1 / median", "cpu": r["cpu"]}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -485,7 +508,9 @@ def main():
     ap.add_argument("--log-m", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="both", choices=["both", "shard", "replicas"])
-    ap.add_argument("--cpu-sample-log-m", type=int, default=17)
+    ap.add_argument("--cpu-budget-s", type=float, default=200.0, help="--impl reference: bound on the summed prover time")
+    ap.add_argument("--flavour", default="field", choices=["field", "binary"],
+                    help="R1CS generator: r1cs_examples.tcc:25-93 (uniform field witness) or :100-157 (0/1 witness)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--window", type=int, default=0, help="window size c of the key's fixed-base tables (0 = cost model)")
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (b200_set_option), repeatable")

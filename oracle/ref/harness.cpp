@@ -5,7 +5,8 @@
 //   u64 nc, ni, nv, n_coeffs; coeffs (32 B mont each); for A, B, C: u64 nnz, row_ptr[nc+1] u64, col[nnz] u32, cidx[nnz] u32;
 //   witness (nv+1) x 32 B mont; u64 pk_len; pk bytes (ALT_NOZK layout = the reference's own operator<< under these flags)
 // Output file: A.x A.y | B.x.c0 B.x.c1 B.y.c0 B.y.c1 | C.x C.y as 32-byte standard-form little-endian integers, then
-// u64 m, then aH[0..m) (mont), then double seconds (the prover call, as "Call to r1cs_gg_ppzksnark_zok_prover").
+// u64 m, then aH[0..m) (mont), then double seconds (the fastest prover call, as "Call to r1cs_gg_ppzksnark_zok_prover"),
+// then u64 repeats and the duration of every repeat in call order (doubles), so that callers can report mean / median.
 #include <fstream>
 #include <iostream>
 #include <sstream>
@@ -25,8 +26,12 @@ static FieldT rd_fr(std::istream& in) { FieldT f; in.read((char*)f.mont_repr.dat
 template <typename F> static void wr_std(std::ostream& out, const F& f) { auto b = f.as_bigint(); out.write((const char*)b.data, 32); }
 
 int main(int argc, char** argv) {
-    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats]\n"; return 2; }
+    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats [budget_seconds min_repeats]]\n"; return 2; }
     const int repeats = argc > 3 ? atoi(argv[3]) : 1;
+    // optional bound for benchmark runs: stop before `repeats` once the prover calls have used budget_seconds, but not
+    // before min_repeats of them ran (the number that ran is written to the output)
+    const double budget = argc > 5 ? atof(argv[4]) : 0.0;
+    const int min_repeats = argc > 5 ? atoi(argv[5]) : repeats;
     ppT::init_public_params();
     libff::inhibit_profiling_info = true;
     libff::inhibit_profiling_counters = true;
@@ -72,12 +77,17 @@ int main(int argc, char** argv) {
     ctx.scratch_exponents.resize(m + nv + 8);
 
     double best = 1e30;
+    std::vector<double> times;
+    double used = 0;
     r1cs_gg_ppzksnark_zok_proof<ppT> proof;
     for (int i = 0; i < repeats; ++i) {
         auto t0 = std::chrono::steady_clock::now();
         proof = r1cs_gg_ppzksnark_zok_prover<ppT>(ctx, w);
         double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         if (dt < best) best = dt;
+        times.push_back(dt);
+        used += dt;
+        if (budget > 0 && used > budget && i + 1 >= min_repeats) break;
     }
     std::ofstream out(argv[2], std::ios::binary);
     auto A = proof.g_A; A.to_affine_coordinates();
@@ -89,5 +99,8 @@ int main(int argc, char** argv) {
     out.write((const char*)&m, 8);
     for (uint64_t i = 0; i < m; ++i) out.write((const char*)ctx.aH[i].mont_repr.data, 32);
     out.write((const char*)&best, 8);
+    const uint64_t nt = times.size();
+    out.write((const char*)&nt, 8);
+    out.write((const char*)times.data(), 8 * nt);
     return 0;
 }

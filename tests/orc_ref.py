@@ -58,19 +58,26 @@ def write_problem(path, circ, w, pk_alt_nozk_bytes):
         f.write(pk_alt_nozk_bytes)
 
 
-def prove(circ, w, key, repeats=1, threads=None):
-    """returns ((A, B, C, inf) in the oracle's layout, H coefficients (m, 4) Montgomery, seconds)"""
+def prove(circ, w, key, repeats=1, threads=None, all_times=False, budget_s=None, min_repeats=None):
+    """returns ((A, B, C, inf) in the oracle's layout, H coefficients (m, 4) Montgomery, seconds); seconds = the fastest
+    repeat, or with all_times the list of every repeat's duration in call order"""
     with tempfile.TemporaryDirectory() as d:
         prob, out = os.path.join(d, "problem.bin"), os.path.join(d, "out.bin")
         write_problem(prob, circ, w, key.serialize(orc.FMT_ALT_NOZK))
         env = dict(os.environ)
         if threads:
             env["OMP_NUM_THREADS"] = str(threads)
-        subprocess.run([REF_BIN, prob, out, str(repeats)], check=True, env=env, stdout=subprocess.DEVNULL)
+        cmd = [REF_BIN, prob, out, str(repeats)]
+        if budget_s:
+            cmd += [str(float(budget_s)), str(int(min_repeats or 1))]
+        subprocess.run(cmd, check=True, env=env, stdout=subprocess.DEVNULL)
         raw = open(out, "rb").read()
     pts = np.frombuffer(raw[:8 * 32], dtype=np.uint64).reshape(8, 4)
     A = pts[0:2].reshape(-1).copy(); B = pts[2:6].reshape(-1).copy(); Cc = pts[6:8].reshape(-1).copy()
     m = struct.unpack("<Q", raw[256:264])[0]
     h = np.frombuffer(raw[264:264 + 32 * m], dtype=np.uint64).reshape(m, 4).copy()
     sec = struct.unpack("<d", raw[264 + 32 * m:272 + 32 * m])[0]
+    if all_times:
+        nt = struct.unpack("<Q", raw[272 + 32 * m:280 + 32 * m])[0]
+        sec = list(struct.unpack("<%dd" % nt, raw[280 + 32 * m:280 + 32 * m + 8 * nt]))
     return (A, B, Cc, np.zeros(3, np.uint8)), h, sec
