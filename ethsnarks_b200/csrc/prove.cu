@@ -288,8 +288,9 @@ int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt,
         rd.point(2, c2 + 128);      // delta_g2
         k->consts_g1 = dev_upload_bytes(c1, sizeof c1);
         k->consts_g2 = dev_upload_bytes(c2, sizeof c2);
-        // A query: sparse_vector<G1>
-        k->domain_size = rd.number();
+        // A query: sparse_vector<G1> in the _nozk key
+        const uint8_t* after_consts = rd.p;
+        if (!k->full) k->domain_size = rd.number();
         auto read_sparse = [&](bool is_b, std::vector<uint32_t>& idx, std::vector<uint8_t>& v1, std::vector<uint8_t>& v2) {
             const uint64_t n_idx = rd.number();
             std::vector<uint64_t> all_idx(n_idx);
@@ -316,7 +317,26 @@ int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt,
                 if (keep) idx[i - lo] = (uint32_t)all_idx[i];
             }
         };
-        {
+        if (k->full) {
+            // un-stripped key: A is a dense libff::G1_vector (…zok.hpp:85, `out << pk.A_query` …zok.tcc:61) - a count and one
+            // point per variable, zeros included, no domain size and no index list; its length is the domain size
+            rd.p = after_consts;
+            const uint64_t n = rd.number();
+            k->domain_size = n;
+            uint64_t lo, hi;
+            shard_range(n, rank, world, lo, hi);
+            std::vector<uint32_t> idx(hi - lo);
+            std::vector<uint8_t> v1((hi - lo) * 64);
+            uint8_t scratch[64];
+            for (uint64_t i = 0; i < n; ++i) {
+                const bool keep = (i >= lo && i < hi);
+                rd.point(1, keep ? &v1[(i - lo) * 64] : scratch);
+                if (keep) idx[i - lo] = (uint32_t)i;
+            }
+            k->nA = idx.size();
+            k->A_idx = dev_upload(idx);
+            k->A = dev_upload_bytes(v1.data(), v1.size());
+        } else {
             std::vector<uint32_t> idx; std::vector<uint8_t> v1, v2;
             read_sparse(false, idx, v1, v2);
             k->nA = idx.size();
@@ -396,7 +416,7 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
                         b200_key** out) {
     if (!ctx || !A || !B_g2 || !H || !L || !g1c || !g2c || !out) return B200_ERR_ARG;
     if (A->group != 1 || B_g2->group != 2 || H->group != 1 || L->group != 1 || (B_g1 && (B_g1->group != 1 || B_g1->n != B_g2->n))) return B200_ERR_ARG;
-    if (L->n > num_variables - num_inputs) return B200_ERR_ARG;
+    if (num_inputs > num_variables || L->n > num_variables - num_inputs) return B200_ERR_ARG;
     return Guard{ctx}.run([&] {
         std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
         k->ctx = ctx; k->owns_bases = false; k->full = B_g1 != nullptr;
@@ -495,6 +515,10 @@ int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b
         if (logm < 1) logm = 1;
         k->logm = logm; k->m = (uint64_t)1 << logm;
         if (k->H_total + 1 < k->m) throw std::invalid_argument("circuit_load: H query shorter than domain size - 1");
+        // the L MSM reads nL scalars from w[ni + 1 + L_lo ...]; the A / B gathers index w[0..nv] (…zok.tcc:487-531)
+        if (k->L_lo + k->nL > k->nv - k->ni) throw std::invalid_argument("circuit_load: L query longer than num_variables - num_inputs");
+        if (k->world == 1 && k->nL != k->nv - k->ni) throw std::invalid_argument("circuit_load: L query length differs from num_variables - num_inputs");
+        if (k->nA > k->nv + 1 || k->nB > k->nv + 1) throw std::invalid_argument("circuit_load: A or B query longer than num_variables + 1");
         for (int i = 0; i < 3; ++i) csr_upload(ctx, mats[i]->row_ptr, mats[i]->col, mats[i]->coeff_idx, mats[i]->n_rows, &k->M[i]);
         k->coeffs = dev_upload_bytes((const uint8_t*)coeffs, n_coeffs * 32);
         domain_create(ctx, logm, &k->dom);

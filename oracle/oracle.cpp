@@ -541,7 +541,10 @@ static Key* genkey(const Circuit& c, u64 seed_base) {
 static void put_g1(std::string& o, const AffG1& p, bool alt) {
     o.push_back(p.inf ? '1' : '0');
     if (alt) {
-        o.append((const char*)p.x.v, 32); o.append((const char*)p.y.v, 32);
+        // libff writes the affine copy of the point; zero is (0, 1, 0) (alt_bn128_g1.cpp:404-417, alt_bn128_init.cpp G1_zero)
+        u64 z[4] = {0, 0, 0, 0};
+        if (p.inf) { o.append((const char*)z, 32); o.append((const char*)Fq::P.one, 32); }
+        else { o.append((const char*)p.x.v, 32); o.append((const char*)p.y.v, 32); }
     } else {
         u64 z[4] = {0, 0, 0, 0};
         if (p.inf) { o.append((const char*)z, 32); o.append((const char*)z, 32); o.append((const char*)z, 32); }
@@ -551,8 +554,12 @@ static void put_g1(std::string& o, const AffG1& p, bool alt) {
 static void put_g2(std::string& o, const AffG2& p, bool alt) {
     o.push_back(p.inf ? '1' : '0');
     if (alt) {
-        o.append((const char*)p.x.a.v, 32); o.append((const char*)p.x.b.v, 32);
-        o.append((const char*)p.y.a.v, 32); o.append((const char*)p.y.b.v, 32);
+        u64 z[4] = {0, 0, 0, 0};
+        if (p.inf) { o.append((const char*)z, 32); o.append((const char*)z, 32); o.append((const char*)Fq::P.one, 32); o.append((const char*)z, 32); }
+        else {
+            o.append((const char*)p.x.a.v, 32); o.append((const char*)p.x.b.v, 32);
+            o.append((const char*)p.y.a.v, 32); o.append((const char*)p.y.b.v, 32);
+        }
     } else {
         u64 z[4] = {0, 0, 0, 0};
         if (p.inf) { for (int i = 0; i < 6; ++i) o.append((const char*)z, 32); }
@@ -570,10 +577,21 @@ static std::string serialize_key(const Key& K, int fmt) {
     std::string o;
     put_g1(o, K.alpha_g1, alt); put_g1(o, K.beta_g1, alt); put_g2(o, K.beta_g2, alt);
     put_g1(o, K.delta_g1, alt); put_g2(o, K.delta_g2, alt);
-    put_num(o, K.domain_size); put_num(o, K.A_idx.size());
-    for (u64 i : K.A_idx) put_num(o, i);
-    put_num(o, K.A_val.size());
-    for (auto& p : K.A_val) put_g1(o, p, alt);
+    if (full) {
+        // the un-stripped key holds A as a dense libff::G1_vector (…zok.hpp:85, built at …zok.tcc:387, written with
+        // `out << pk.A_query`, …zok.tcc:61): a count and then one point per variable, zeros included, no index list
+        put_num(o, K.domain_size);
+        AffG1 zero; zero.inf = true;
+        size_t j = 0;
+        for (u64 i = 0; i < K.domain_size; ++i) {
+            if (j < K.A_idx.size() && K.A_idx[j] == i) put_g1(o, K.A_val[j++], alt); else put_g1(o, zero, alt);
+        }
+    } else {
+        put_num(o, K.domain_size); put_num(o, K.A_idx.size());
+        for (u64 i : K.A_idx) put_num(o, i);
+        put_num(o, K.A_val.size());
+        for (auto& p : K.A_val) put_g1(o, p, alt);
+    }
     put_num(o, K.domain_size); put_num(o, K.B_idx.size());
     for (u64 i : K.B_idx) put_num(o, i);
     put_num(o, K.B_val.size());

@@ -1,14 +1,15 @@
-// oracle/_ref circuit dumper — TEST INFRASTRUCTURE ONLY.  Builds a circuit with the REFERENCE's own gadget code, compiled
-// from the sources where they lie under /root/reference, and writes its constraint system and witness in the problem
-// format of harness.cpp / tests/orc_ref.py (with pk_len = 0), so that the same R1CS + witness can be proved by the
-// reference prover (ref_prove), the oracle and the GPU library.
-//   circuit_dump sha256 <out>   BASELINE.json configs[1]: sha256_full_gadget_512 (src/gadgets/sha256_full.hpp:69-163) on the
-//                               input of src/test/test_sha256_full_gadget.cpp:30-99: block = sha256("test") || sha256("test"),
-//                               digest bits made the primary input; prints the digest (KAT D294F6E5..., :48-52)
-//   circuit_dump mimc_merkle <out>  BASELINE.json configs[0]: merkle_path_authenticator<MiMC_e7_hash_gadget> of depth 29
-//                               (src/gadgets/merkle_tree.hpp:70-192, src/gadgets/mimc.hpp), root public.  First reproduces
-//                               the reference's depth-1 known answer (src/test/test_merkle_tree.cpp:56-62), which pins the
-//                               MiMC round constants (and with them the sha3.h stand-in's padding flavour).
+// Circuit builders shared by oracle/_ref/circuit_dump and oracle/_ref/shim_prove — TEST INFRASTRUCTURE ONLY.  Each builds one
+// BASELINE.json circuit with the REFERENCE's own gadget code, compiled from the sources where they lie under /root/reference,
+// generates its witness, and hands the protoboard to g_emit (the dumper writes the problem file, the shim harness proves it).
+//   sha256       BASELINE.json configs[1]: sha256_full_gadget_512 (src/gadgets/sha256_full.hpp:69-163) on the
+//                input of src/test/test_sha256_full_gadget.cpp:30-99: block = sha256("test") || sha256("test"),
+//                digest bits made the primary input; prints the digest (KAT D294F6E5..., :48-52)
+//   mimc_merkle  BASELINE.json configs[0]: merkle_path_authenticator<MiMC_e7_hash_gadget> of depth 29
+//                (src/gadgets/merkle_tree.hpp:70-192, src/gadgets/mimc.hpp), root public.  First reproduces
+//                the reference's depth-1 known answer (src/test/test_merkle_tree.cpp:56-62), which pins the
+//                MiMC round constants (and with them the sha3.h stand-in's padding flavour).
+//   eddsa        BASELINE.json configs[2], see build_eddsa
+#pragma once
 #include <fstream>
 #include <iostream>
 #include <cstring>
@@ -22,36 +23,8 @@
 using namespace ethsnarks;
 using libsnark::ConstantStorage;
 
-template <typename T> static void wr(std::ostream& out, const T& v) { out.write((const char*)&v, sizeof(T)); }
 
-static void dump(ProtoboardT& pb, const char* path) {
-    const auto& cs = pb.constraint_system;
-    const uint64_t nc = cs.constraints.size(), ni = pb.num_inputs(), nv = pb.num_variables();
-    const auto& consts = ConstantStorage<FieldT>::getInstance().constants;
-    const uint64_t ncoef = consts.size();
-    std::ofstream out(path, std::ios::binary);
-    wr(out, nc); wr(out, ni); wr(out, nv); wr(out, ncoef);
-    for (const auto& c : consts) out.write((const char*)c.mont_repr.data, 32);
-    for (int k = 0; k < 3; ++k) {
-        std::vector<uint64_t> rp(nc + 1, 0);
-        std::vector<uint32_t> col, ci;
-        for (uint64_t r = 0; r < nc; ++r) {
-            const auto lc = k == 0 ? cs.constraints[r]->getA() : k == 1 ? cs.constraints[r]->getB() : cs.constraints[r]->getC();
-            for (const auto& t : lc.getTerms()) { col.push_back((uint32_t)t.index); ci.push_back((uint32_t)t.coeff_index); }
-            rp[r + 1] = col.size();
-        }
-        const uint64_t nnz = col.size();
-        wr(out, nnz);
-        out.write((const char*)rp.data(), 8 * (nc + 1));
-        out.write((const char*)col.data(), 4 * nnz);
-        out.write((const char*)ci.data(), 4 * nnz);
-    }
-    // in this fork pb.values[0] is the constant 1 (protoboard.tcc:24-31), so pb.values IS the full assignment (1, x)
-    for (const auto& v : pb.values) out.write((const char*)v.mont_repr.data, 32);
-    const uint64_t pk_len = 0;
-    wr(out, pk_len);
-    std::cout << "constraints " << nc << " variables " << nv << " inputs " << ni << " satisfied " << pb.is_satisfied() << "\n";
-}
+static int (*g_emit)(ethsnarks::ProtoboardT& pb, const char* arg) = nullptr;
 
 static int build_sha256(const char* path) {
     using namespace libsnark;
@@ -77,7 +50,7 @@ static int build_sha256(const char* path) {
     std::cout << "digest ";
     for (size_t i = 0; i < SHA256_digest_size_bytes; ++i) printf("%02X", got[i]);
     std::cout << (memcmp(got, output_digest, sizeof got) == 0 ? " == openssl-style SHA256" : " MISMATCH") << "\n";
-    dump(pb, path);
+    g_emit(pb, path);
     return pb.is_satisfied() && memcmp(got, output_digest, sizeof got) == 0 ? 0 : 1;
 }
 
@@ -105,7 +78,7 @@ static int build_eddsa(const char* path_out) {
     the_gadget.generate_r1cs_constraints();
     the_gadget.generate_r1cs_witness();
     pb.set_input_sizes(2);
-    dump(pb, path_out);
+    g_emit(pb, path_out);
     return pb.is_satisfied() ? 0 : 1;
 }
 
@@ -145,22 +118,20 @@ static int build_mimc_merkle(const char* path_out) {
     auth.generate_r1cs_constraints();
     pb.set_input_sizes(1);
     std::cout << "root "; pb.val(expected_root).as_bigint().print();
-    dump(pb, path_out);
+    g_emit(pb, path_out);
     return auth.is_valid() && pb.is_satisfied() ? 0 : 1;
 }
 
-int main(int argc, char** argv) {
-    if (argc < 3) { std::cerr << "usage: circuit_dump sha256|mimc_merkle|eddsa <out>\n"; return 2; }
-    ppT::init_public_params();
-    libff::inhibit_profiling_info = true;
-    libff::inhibit_profiling_counters = true;
-    if (!strcmp(argv[1], "sha256")) return build_sha256(argv[2]);
-    if (!strcmp(argv[1], "eddsa")) return build_eddsa(argv[2]);
-    if (!strcmp(argv[1], "mimc_merkle")) {
-        // the padding flavour of the absent SHA3IUF fork is decided by the reference's own known answer
+
+// builds `name` and emits it with `arg`; the padding flavour of the absent SHA3IUF fork is decided by the reference's own
+// known answer
+static int build_circuit(const char* name, const char* arg) {
+    if (!strcmp(name, "sha256")) return build_sha256(arg);
+    if (!strcmp(name, "eddsa")) return build_eddsa(arg);
+    if (!strcmp(name, "mimc_merkle")) {
         for (unsigned char pad : {(unsigned char)0x01, (unsigned char)0x06}) {
             b200_shim_sha3_pad() = pad;
-            if (merkle_kat()) { std::cout << "sha3 padding byte " << (int)pad << "\n"; return build_mimc_merkle(argv[2]); }
+            if (merkle_kat()) { std::cout << "sha3 padding byte " << (int)pad << "\n"; return build_mimc_merkle(arg); }
         }
         std::cerr << "no padding flavour reproduces the reference's Merkle known answer\n";
         return 1;

@@ -26,7 +26,21 @@ static FieldT rd_fr(std::istream& in) { FieldT f; in.read((char*)f.mont_repr.dat
 template <typename F> static void wr_std(std::ostream& out, const F& f) { auto b = f.as_bigint(); out.write((const char*)b.data, 32); }
 
 int main(int argc, char** argv) {
-    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats [budget_seconds min_repeats]]\n"; return 2; }
+    if (argc == 4 && std::string(argv[1]) == "--roundtrip-full") {
+        // pins the byte layout of the UN-STRIPPED key: the reference's own operator>> for r1cs_gg_ppzksnark_zok_proving_key
+        // (…zok.tcc:69-87) reads the file, its operator<< (…zok.tcc:54-66) writes it back; tests compare the bytes
+        ppT::init_public_params();
+        std::ifstream kin(argv[2], std::ios::binary);
+        if (!kin) { std::cerr << "cannot open key file\n"; return 2; }
+        r1cs_gg_ppzksnark_zok_proving_key<ppT> full;
+        kin >> full;
+        std::ofstream kout(argv[3], std::ios::binary);
+        kout << full;
+        std::cout << "A " << full.A_query.size() << " B " << full.B_query.size() << " of " << full.B_query.domain_size() << " H " << full.H_query.size()
+                  << " L " << full.L_query.size() << "\n";
+        return 0;
+    }
+    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats [budget_seconds min_repeats]] | --roundtrip-full <pk_in> <pk_out>\n"; return 2; }
     const int repeats = argc > 3 ? atoi(argv[3]) : 1;
     // optional bound for benchmark runs: stop before `repeats` once the prover calls have used budget_seconds, but not
     // before min_repeats of them ran (the number that ran is written to the output)

@@ -116,6 +116,15 @@ def test_ntt_radix4_passes(ctx, logm):
             assert np.array_equal(got, want), (logm, mode, r4)
 
 
+@pytest.mark.parametrize("logm,modes", [(20, (0, 1, 2, 3)), (22, (0, 3))])
+def test_ntt_large_vs_oracle(ctx, logm, modes):
+    """b200_ntt bit-for-bit against the oracle's transform at the sizes whose pass plan differs from the small cases
+    (three shared-memory passes at 2^20 - 2^24)."""
+    x = orc.sha512_rng_fr(13 * logm, 1 << logm)
+    for mode in modes:
+        assert np.array_equal(ctx.ntt(x, logm, mode), orc.ntt(x, logm, mode)), (logm, mode)
+
+
 def test_ntt_large_roundtrip_and_linearity(ctx):
     logm = 20
     n = 1 << logm
@@ -662,6 +671,49 @@ def test_prove_full_size_2p20_identical_to_oracle(ctx):
     assert key.check_in_exponent(w, got) == 0
     assert np.array_equal(pk.h_poly(w), circ.h_poly(w)[:circ.m])
     pk.free()
+
+
+def _full_size_device_key_vs_oracle(ctx, circ):
+    """device-generated key (same toxic waste as the oracle's generator => the same key) against the oracle's prove:
+    H coefficients and the three proof points bit-identical, plus the closed form in the exponent"""
+    w = circ.witness()
+    key = orc.Key(circ)
+    mats = [circ.matrix(i) for i in range(3)]
+    gk, vk = eb.ProvingKey.generate(ctx, mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv, orc.sha512_rng_fr(1 << 32, 5))
+    assert eb.host.vk_to_json(vk) == key.vk_json()
+    gk.load_circuit(mats[0], mats[1], mats[2], circ.coeffs(), circ.ni, circ.nv)
+    del mats
+    got = gk.prove(w)
+    want = key.prove(w)
+    for g, e in zip(got, want):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    assert key.check_in_exponent(w, got) == 0
+    assert np.array_equal(gk.h_poly(w), circ.h_poly(w)[:circ.m])
+    return gk, key, w, got
+
+
+def test_prove_binary_witness_2p20_identical_to_oracle(ctx):
+    """SURVEY 8(d)'s second R1CS flavour at full size: generate_r1cs_example_with_binary_input (r1cs_examples.tcc:100-157),
+    every witness value 0 or 1 - all "1" scalars fall into ONE bucket, the case the reference's 0/1 prefilter
+    (multiexp.tcc:668-701) exists for and the block-per-bucket finalize carries here."""
+    circ = orc.Circuit.synth_binary((1 << 20) - 2, 1)
+    assert circ.m == 1 << 20
+    gk, key, w, got = _full_size_device_key_vs_oracle(ctx, circ)
+    # the same through the reference's pk byte layout (sparse A / B queries: variables the matrices never touch are absent)
+    pk = _load(ctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
+    for g, e in zip(pk.prove(w), got):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    pk.free()
+    gk.free()
+
+
+@pytest.mark.skipif(not os.environ.get("B200_SLOW_TESTS"), reason="several minutes of CPU oracle work: set B200_SLOW_TESTS=1")
+def test_prove_full_size_2p24_identical_to_oracle(ctx):
+    """BASELINE.json configs[3] at 2^24 constraints: H coefficients and the proof bit-identical to the oracle's."""
+    circ = orc.Circuit.synth_field((1 << 24) - 2, 1)
+    assert circ.m == 1 << 24
+    gk, key, w, got = _full_size_device_key_vs_oracle(ctx, circ)
+    gk.free()
 
 
 def test_key_cache_round_trip(ctx):

@@ -156,6 +156,25 @@ def test_reference_build_reads_the_oracle_key_bytes_and_matches_golden():
     assert orc.proof_json(proof, w[1:1 + c.ni]) == GOLD["circuits"]["field_30_3"]["proof_json"]
 
 
+@needs_ref
+def test_full_key_layout_is_the_reference_layout():
+    """B200_FMT_ALT_FULL is the byte stream of the reference's UN-STRIPPED key: the reference's own operator>> for
+    r1cs_gg_ppzksnark_zok_proving_key (dense G1_vector A, knowledge-commitment B) reads the oracle's ALT_FULL bytes and its
+    operator<< writes back exactly the same bytes.  A witness that leaves A-query entries at zero makes the dense layout
+    differ from the sparse one."""
+    import subprocess, tempfile
+    c = orc.Circuit.synth_binary(40, 3); k = orc.Key(c)
+    blob = k.serialize(orc.FMT_ALT_FULL)
+    with tempfile.TemporaryDirectory() as d:
+        a, b = os.path.join(d, "full.raw"), os.path.join(d, "back.raw")
+        open(a, "wb").write(blob)
+        res = subprocess.run([orc_ref.REF_BIN, "--roundtrip-full", a, b], check=True, capture_output=True, text=True)
+        assert open(b, "rb").read() == blob
+    dims = res.stdout.split()
+    assert int(dims[1]) == c.nv + 1          # A dense over all variables + ONE
+    assert len(blob) != len(k.serialize(orc.FMT_ALT_NOZK)) + 64 * int(dims[3])   # not the sparse layout with G1 halves added
+
+
 @pytest.mark.skipif(not (orc_ref.available() and orc_ref.dump_available()), reason="oracle/_ref not built (needs /root/reference)")
 @pytest.mark.parametrize("name", ["sha256", "mimc_merkle", "eddsa"])
 def test_reference_gadget_circuits_oracle_equals_reference_prover(name):
