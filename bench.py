@@ -43,20 +43,37 @@ def shard_range(n, rank, world):
     return n * rank // world, n * (rank + 1) // world
 
 
-def gather_partials(part, flags, world, device="cuda"):
-    """all_gather of one rank's (32 limbs, 3 flags) -> (world, 32) uint64, (world, 3) uint8, in rank order."""
+def all_gather_packed(parts, part, stream=None):
+    """rank r's 256-byte record `part` (32 x int64) lands at parts[32 r : 32 r + 32] on every rank; on `stream` when given"""
     import torch
     import torch.distributed as dist
-    if world == 1:
-        return part.reshape(1, 32), flags.reshape(1, 3)
-    buf = np.zeros(35, dtype=np.int64)
-    buf[:32] = part.view(np.int64)
-    buf[32:] = flags
-    t = torch.from_numpy(buf).to(device)
-    out = [torch.zeros_like(t) for _ in range(world)]
-    dist.all_gather(out, t)
-    allb = torch.stack(out).cpu().numpy()
-    return np.ascontiguousarray(allb[:, :32]).view(np.uint64), np.ascontiguousarray(allb[:, 32:].astype(np.uint8))
+    if stream is None:
+        dist.all_gather_into_tensor(parts, part)
+    else:
+        with torch.cuda.stream(stream):
+            dist.all_gather_into_tensor(parts, part)
+
+
+class ShardedProver:
+    """One proof over a key sharded 1/N per rank, with the exchange on the device: every rank queues its partial proof
+    (b200_prove_partial_dev: 256 B left in HBM, no synchronisation), the records are all-gathered over NCCL on the library's
+    own stream, and rank 0 combines them (b200_proof_combine_dev) and copies the proof back - one host synchronisation per
+    proof, on rank 0 only."""
+
+    def __init__(self, key, world, rank, stream, dev):
+        import torch
+        self.key, self.world, self.rank, self.stream = key, world, rank, stream
+        self.part = torch.zeros(32, dtype=torch.int64, device=dev)             # 256 B: A 64 | B 128 | C 64
+        self.parts = torch.zeros(32 * world, dtype=torch.int64, device=dev)
+
+    def __call__(self, wptr):
+        self.key.prove_partial_dev(wptr, self.part.data_ptr())
+        if self.world > 1:
+            all_gather_packed(self.parts, self.part, self.stream)
+            src = self.parts
+        else:
+            src = self.part
+        return self.key.combine_dev(src.data_ptr(), self.world) if self.rank == 0 else None
 
 
 def max_over_ranks(x, device="cuda"):
@@ -276,7 +293,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    shard = world > 1 and args.mode == "shard"
+    shard = world > 1 and args.mode in ("both", "shard")          # headline at N > 1: ONE proof over a key sharded 1/N (strong scaling)
     ctx = eb.Context(local)
     imad_peak = ctx.imad_peak(5)
     if args.window:
@@ -304,30 +321,19 @@ def run_ours(args):
         barrier()
         return max_over_ranks(e0.elapsed_time(e1), dev), ctx.launches - l0
 
-    # the other N>1 arrangement, measured in the same run and reported beside the headline: one proof with the key
-    # sharded 1/N per GPU (the north-star's MSM split; strong scaling, it shortens the latency of ONE proof)
-    sharded = None
-    if world > 1 and args.mode == "both":
-        skey, switness, sdims = build_workload(eb, ctx, args.log_m, rank, world, args.flavour)
-        sw_dev = torch.from_numpy(switness.view(np.int64)).to(dev)
-
-        def sstep():
-            part, flags = skey.prove_partial(sw_dev.data_ptr())
-            parts, fl = gather_partials(part, flags, world, device=dev)
-            return skey.combine(parts, fl) if rank == 0 else None
+    # the other N > 1 arrangement, measured in the same run and reported beside the headline: N independent replicas, every
+    # rank proving its own witnesses against a whole resident key (weak scaling, no data-path collective)
+    replicas = None
+    if world > 1 and args.mode == "both" and args.log_m <= 22:
+        rkey, rwitness, _ = build_workload(eb, ctx, args.log_m, 0, 1, args.flavour)
+        rw_dev = torch.from_numpy(rwitness.view(np.int64)).to(dev)
         for _ in range(max(args.warmup, 3)):
-            sstep()
-        sms, _ = timed_steps(sstep, args.steps)
-        sharded = {"scaling": "strong", "parallelism": "key sharded 1/%d per GPU, 35x8 B partial sums all-gathered over NCCL" % world,
-                   "latency_ms": sms / args.steps, "proofs_per_sec": args.steps / (sms * 1e-3)}
-        if args.verify:
-            sproof = sstep()
-            torch.cuda.synchronize()
-            if rank == 0:
-                sharded["verified_in_the_exponent"] = verify_in_the_exponent(eb, ctx, skey, switness, sproof, sdims)
-                if not sharded["verified_in_the_exponent"]:
-                    raise SystemExit("bench.py: the sharded proof does not match its closed form in the exponent")
-        del skey, sw_dev
+            rkey.prove(rw_dev.data_ptr())
+        rms, _ = timed_steps(lambda: rkey.prove(rw_dev.data_ptr()), args.steps)
+        replicas = {"scaling": "weak", "parallelism": "%d independent replicas, a whole key per GPU, no collective" % world,
+                    "ms_per_step": rms / args.steps, "proofs_per_sec": world * args.steps / (rms * 1e-3)}
+        rkey.free()
+        del rkey, rw_dev
         torch.cuda.synchronize()
 
     key, witness, dims = build_workload(eb, ctx, args.log_m, rank if shard else 0, world if shard else 1, args.flavour)
@@ -335,12 +341,10 @@ def run_ours(args):
     w_dev = torch.from_numpy(witness.view(np.int64)).to(dev)            # resident witness (`value`)
     w_pin = torch.from_numpy(witness.view(np.int64)).pin_memory()       # pinned host witness (`e2e`)
 
+    sharded_prove = ShardedProver(key, world, rank, stream, dev) if shard else None
+
     def step(wptr):
-        if shard:
-            part, flags = key.prove_partial(wptr)
-            parts, fl = gather_partials(part, flags, world, device=dev)
-            return key.combine(parts, fl) if rank == 0 else None
-        return key.prove(wptr)
+        return sharded_prove(wptr) if shard else key.prove(wptr)
 
     def timed(wptr, steps, collect):
         return timed_steps(lambda: step(wptr), steps, collect)
@@ -421,6 +425,19 @@ def run_ours(args):
             verified = verify_in_the_exponent(eb, ctx, key, witness, proof, dims)
             if not verified:
                 raise SystemExit("bench.py: the proof does not match its closed form in the exponent")
+    # the N-rank proof must be the proof one GPU gives: rank 0 proves the same witness against the whole key and compares bytes
+    identical_to_one_gpu = None
+    if shard and args.verify:
+        proof_n = step(w_dev.data_ptr())
+        torch.cuda.synchronize()
+        if rank == 0:
+            key1, _, _ = build_workload(eb, ctx, args.log_m, 0, 1, args.flavour)
+            proof_1 = key1.prove(w_dev.data_ptr())
+            identical_to_one_gpu = all(np.array_equal(np.asarray(a), np.asarray(b)) for a, b in zip(proof_n, proof_1))
+            key1.free()
+            if not identical_to_one_gpu:
+                raise SystemExit("bench.py: the %d-GPU sharded proof differs from the one-GPU proof" % world)
+        barrier()
     proofs = args.steps * (1 if (shard or world == 1) else world)
     value = proofs / (ms_dev * 1e-3)
     e2e = proofs / (ms_e2e * 1e-3)
@@ -477,7 +494,7 @@ def run_ours(args):
         "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "strong" if shard else "weak", "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery)", "data": "synthetic",
         "config": {**workload_config(args.log_m, args.flavour), "num_inputs": dims["ni"], "msm_lengths": {"A": dims["nA"], "B_g2": dims["nB"], "H": dims["nH"], "L": dims["nL"]},
-                   "parallelism": ("key sharded 1/%d per GPU, partial sums all-gathered" % world) if shard else
+                   "parallelism": ("ONE proof over a key sharded 1/%d per GPU; 256-byte partial sums all-gathered over NCCL on the device" % world) if shard else
                                   (("%d independent replicas" % world if world > 1 else "single GPU") +
                                    (", %d proofs in flight per GPU on one resident key" % len(slots) if len(slots) > 1 else "")),
                    "l2": "inputs larger than L2 (key + sort buffers >> 126 MB per prove)", "r_s": "0,0 (reference no-ZK prover)"},
@@ -489,8 +506,10 @@ def run_ours(args):
         "msm_subphases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" in k},
         "msm_kernels": kernels, "verified_in_the_exponent": verified,
     }
-    if sharded:
-        line["sharded"] = sharded
+    if replicas:
+        line["replicas"] = replicas
+    if identical_to_one_gpu is not None:
+        line["sharded_proof_identical_to_one_gpu"] = identical_to_one_gpu
     if world == 1 and not args.no_cpu_baseline:
         r = cpu_prove(args.log_m, 3, 1, 30.0, args.flavour)        # bounded: 1 warm-up + 3 timed whole proves of this instance
         line["cpu_baseline"] = {"value": 1.0 / float(np.median(r["times"])), "unit": "proofs/s", "cores": r["threads"], "kind": r["kind"],

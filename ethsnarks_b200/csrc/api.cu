@@ -7,8 +7,59 @@
 #include <cstdio>
 #include <algorithm>
 #include <memory>
+#include <thread>
+#include <mutex>
+#include <condition_variable>
 
 using namespace b200;
+
+// ------------------------------------------------------------------------------------------------ peer-device workers
+struct b200_ctx::Worker::Impl {
+    std::thread th;
+    std::mutex m;
+    std::condition_variable cv;
+    std::function<void()> job;
+    bool has_job = false, busy = false, quit = false;
+    std::exception_ptr err;
+};
+b200_ctx::Worker::Worker(int device) : impl(new Impl()) {
+    impl->th = std::thread([this, device] {
+        cudaSetDevice(device);
+        std::unique_lock<std::mutex> lk(impl->m);
+        for (;;) {
+            impl->cv.wait(lk, [this] { return impl->has_job || impl->quit; });
+            if (impl->quit) return;
+            std::function<void()> job = std::move(impl->job);
+            impl->has_job = false;
+            lk.unlock();
+            std::exception_ptr e;
+            try { job(); } catch (...) { e = std::current_exception(); }
+            lk.lock();
+            impl->err = e;
+            impl->busy = false;
+            impl->cv.notify_all();
+        }
+    });
+}
+b200_ctx::Worker::~Worker() {
+    { std::lock_guard<std::mutex> lk(impl->m); impl->quit = true; }
+    impl->cv.notify_all();
+    impl->th.join();
+    delete impl;
+}
+void b200_ctx::Worker::start(std::function<void()> job) {
+    std::lock_guard<std::mutex> lk(impl->m);
+    impl->job = std::move(job);
+    impl->has_job = true;
+    impl->busy = true;
+    impl->err = nullptr;
+    impl->cv.notify_all();
+}
+void b200_ctx::Worker::wait() {
+    std::unique_lock<std::mutex> lk(impl->m);
+    impl->cv.wait(lk, [this] { return !impl->busy; });
+    if (impl->err) { std::exception_ptr e = impl->err; impl->err = nullptr; std::rethrow_exception(e); }
+}
 
 // ------------------------------------------------------------------------------------------------ ctx plumbing
 void* b200_ctx::scratch(const char* name, size_t bytes) {
@@ -162,11 +213,48 @@ const char* b200_strerror(int code) {
     }
 }
 
+static int init_one(int dev, b200_ctx** out);
+static void shutdown_one(b200_ctx* ctx);
+
+// n_devices > 1: one context that owns several GPUs of the box ("one handle = one device set").  Keys loaded
+// on it are split 1/N per device and b200_prove runs on all of them from this one process, the per-device partial sums
+// travelling to the first device over peer memory (NVLink); everything else (standalone MSM, NTT, generator) runs on the
+// first device.
 int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
     if (!out) return B200_ERR_ARG;
     *out = nullptr;
-    if (n_devices > 1) return B200_ERR_ARG;
-    int dev = (device_ids && n_devices == 1) ? device_ids[0] : 0;
+    if (n_devices <= 1) return init_one((device_ids && n_devices == 1) ? device_ids[0] : 0, out);
+    if (!device_ids || n_devices > 64) return B200_ERR_ARG;
+    b200_ctx* root = nullptr;
+    int rc = init_one(device_ids[0], &root);
+    if (rc) return rc;
+    cudaEventCreateWithFlags(&root->ev_group, cudaEventDisableTiming);
+    for (int i = 1; i < n_devices; ++i) {
+        b200_ctx* p = nullptr;
+        rc = init_one(device_ids[i], &p);
+        if (rc) { b200_shutdown(root); return rc; }
+        cudaEventCreateWithFlags(&p->ev_group, cudaEventDisableTiming);
+        root->peers.push_back(p);
+        root->workers.push_back(new b200_ctx::Worker(device_ids[i]));
+    }
+    // peer access in both directions between every pair; a pair without it cannot join one context
+    for (int i = 0; i < n_devices; ++i)
+        for (int j = 0; j < n_devices; ++j) {
+            if (device_ids[i] == device_ids[j]) continue;   // a device may be listed more than once (one-GPU tests of this path)
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, device_ids[i], device_ids[j]);
+            if (!can) { root->last_error = "b200_init: no peer access between the devices"; b200_shutdown(root); return B200_ERR_CUDA; }
+            cudaSetDevice(device_ids[i]);
+            cudaError_t e = cudaDeviceEnablePeerAccess(device_ids[j], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { b200_shutdown(root); return B200_ERR_CUDA; }
+            (void)cudaGetLastError();
+        }
+    cudaSetDevice(device_ids[0]);
+    *out = root;
+    return B200_OK;
+}
+static int init_one(int dev, b200_ctx** out) {
+    *out = nullptr;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { (void)cudaGetLastError(); return B200_ERR_CUDA; }
     if (dev < 0 || dev >= count) return B200_ERR_ARG;
@@ -197,6 +285,12 @@ int b200_init(const int* device_ids, int n_devices, b200_ctx** out) {
 }
 void b200_shutdown(b200_ctx* ctx) {
     if (!ctx) return;
+    for (auto* w : ctx->workers) delete w;
+    for (auto* p : ctx->peers) { if (p->ev_group) { cudaSetDevice(p->device); cudaEventDestroy(p->ev_group); } shutdown_one(p); }
+    if (ctx->ev_group) { cudaSetDevice(ctx->device); cudaEventDestroy(ctx->ev_group); }
+    shutdown_one(ctx);
+}
+static void shutdown_one(b200_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     for (auto& kv : ctx->slots) cudaFree(kv.second.p);
@@ -210,9 +304,16 @@ void b200_shutdown(b200_ctx* ctx) {
 }
 const char* b200_last_error(b200_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
 void* b200_stream(b200_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
-unsigned long long b200_launch_count(b200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+unsigned long long b200_launch_count(b200_ctx* ctx) {
+    if (!ctx) return 0;
+    unsigned long long n = ctx->launches;
+    for (auto* p : ctx->peers) n += p->launches;
+    return n;
+}
+int b200_device_count(b200_ctx* ctx) { return ctx ? 1 + (int)ctx->peers.size() : 0; }
 int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     if (!ctx || !name) return B200_ERR_ARG;
+    for (auto* p : ctx->peers) b200_set_option(p, name, value);
     if (!strcmp(name, "window")) ctx->window_override = (int)value;
     else if (!strcmp(name, "chunk")) ctx->chunk_override = (int)value;
     else if (!strcmp(name, "timing")) ctx->timing_enabled = value != 0;
@@ -225,6 +326,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "pair_reduce")) ctx->pair_reduce = (int)value;
     else if (!strcmp(name, "reduce_fold")) ctx->reduce_fold = (int)value;
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
+    else if (!strcmp(name, "finalize_big_seg")) ctx->finalize_big_seg = (int)value;
     else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;

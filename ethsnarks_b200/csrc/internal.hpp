@@ -7,6 +7,7 @@
 #include <vector>
 #include <map>
 #include <stdexcept>
+#include <functional>
 
 struct b200_ctx {
     int device = 0;
@@ -31,6 +32,7 @@ struct b200_ctx {
     int g2_pair = 2;                   // G2 accumulate with one point per lane pair (msm_acc_pair.cuh): 2 = lazy operand forms,
                                        // 1 = strict, 3 = lazy + out-of-line products; 0 = one thread per point
     int finalize_chunks = 1;           // 1 = stitch chunk partial sums with one thread per chunk edge (msm_finalize_chunks)
+    int finalize_big_seg = 1;          // 1 = giant buckets (the "scalar == 1" bucket of real witnesses) summed in two levels
     int ntt_radix4 = 1;                // 1 = NTT passes with two stages per shared-memory round trip (ntt_pass4)
     int shared_sort = 1;               // 1 = the witness MSMs of one prove (A, B, L) consume ONE sorted digit list when their
                                        // queries are dense and their tables share a window size
@@ -49,11 +51,27 @@ struct b200_ctx {
     int overlap = 1;
     bool fixed_table_ready[2] = {false, false};   // generator window tables of the fixed-base kernel (G1, G2) built
     cudaStream_t cur() const { return lane ? lanes[lane] : stream; }
+    // multi-device context (b200_init with n_devices > 1): this is the context of the first device; one more context per
+    // further device, each driven by its own host thread so that the devices' launch sequences are issued concurrently
+    std::vector<b200_ctx*> peers;
+    struct Worker;
+    std::vector<Worker*> workers;      // workers[i] drives peers[i]
+    cudaEvent_t ev_group = nullptr;    // on a peer: "this device's partial sums have arrived in the first device's gather buffer"
 
     void* scratch(const char* name, size_t bytes);   // throws std::runtime_error on failure
     void t_begin(const char* name);
     void t_end();
     void t_collect();
+};
+
+// one persistent host thread bound to one peer device
+struct b200_ctx::Worker {
+    explicit Worker(int device);
+    ~Worker();
+    void start(std::function<void()> job);   // returns at once
+    void wait();                             // rethrows what the job threw
+    struct Impl;
+    Impl* impl;
 };
 
 #define B200_CUDA_CHECK(expr)                                                                                   \
@@ -95,6 +113,8 @@ struct MsmPos {
     void g_precompute_##SUFFIX(b200_ctx* ctx, const void* d_bases, size_t n, int c, void* d_table);                              \
     void g_finish_##SUFFIX(b200_ctx* ctx, const void* d_xyzz_terms, int n_terms, const void* d_affine_terms, int n_affine,       \
                            void* d_out_affine, bool to_std);                                                                     \
+    void g_sum_strided_##SUFFIX(b200_ctx* ctx, const void* d_base, size_t stride, int n, const void* d_extra_affine,             \
+                                void* d_out_affine, bool to_std);                                                                \
     void g_fixed_base_##SUFFIX(b200_ctx* ctx, const void* d_scalars_mont, size_t n, void* d_out_affine);                         \
     void g_add_affine_##SUFFIX(b200_ctx* ctx, const void* d_a, const void* d_b, void* d_out, size_t n);                          \
     void g_scalar_mul_##SUFFIX(b200_ctx* ctx, const void* d_affine_base, const void* d_scalar_mont, void* d_out_xyzz);
@@ -118,6 +138,9 @@ inline void g_precompute(b200_ctx* c, int group, const void* b, size_t n, int wi
 int msm_table_window(size_t n);   // window size the cost model picks for a table over n bases
 inline void g_finish(b200_ctx* c, int group, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {
     if (group == 1) g_finish_g1(c, xt, nx, at, na, out, to_std); else g_finish_g2(c, xt, nx, at, na, out, to_std);
+}
+inline void g_sum_strided(b200_ctx* c, int group, const void* base, size_t stride, int n, const void* extra, void* out, bool to_std) {
+    if (group == 1) g_sum_strided_g1(c, base, stride, n, extra, out, to_std); else g_sum_strided_g2(c, base, stride, n, extra, out, to_std);
 }
 inline void g_fixed_base(b200_ctx* c, int group, const void* s, size_t n, void* out) {
     if (group == 1) g_fixed_base_g1(c, s, n, out); else g_fixed_base_g2(c, s, n, out);
@@ -168,6 +191,9 @@ void csr_upload(b200_ctx* ctx, const uint64_t* row_ptr, const uint32_t* col, con
 void csr_free(DeviceCsr* c);
 // out[row] = sum coeffs[cidx[k]] * w[col[k]]  for row < n_rows
 void spmv(b200_ctx* ctx, const DeviceCsr& M, const void* d_coeffs, const void* d_w, void* d_out);
+// out[j * master.n_rows + r] = master row r through translation table j (r1cs_constraint_light_instance)
+void spmv_instances(b200_ctx* ctx, const DeviceCsr& master, const void* d_coeffs, const void* d_w, const uint32_t* d_tables, uint32_t tlen,
+                    uint64_t n_inst, void* d_out);
 void witness_rows(b200_ctx* ctx, const void* d_w, void* d_a, void* d_b, void* d_c, uint64_t nc, uint64_t ni, uint64_t m);
 
 // --- key generator scalars (gen.cu) -----------------------------------------------------------------------------

@@ -42,6 +42,31 @@ __global__ void g_finish_kernel(const typename G::Pt* xt, int nx, const typename
     *out = a;
     *reinterpret_cast<uint32_t*>(out + 1) = inf;
 }
+// out = sum of n affine points laid out `stride` bytes apart (the gathered per-GPU partial sums of a sharded proof) + an
+// optional extra affine term (alpha_g1 / beta_g2); same output layout as g_finish_kernel
+template <typename G>
+__global__ void g_sum_strided_kernel(const unsigned char* base, size_t stride, int n, const typename G::Aff* extra, typename G::Aff* out, bool to_std) {
+    typedef typename G::Pt Pt;
+    if (threadIdx.x || blockIdx.x) return;
+    Pt r = Pt::inf();
+    for (int i = 0; i < n; ++i) r.add_mixed(*reinterpret_cast<const typename G::Aff*>(base + (size_t)i * stride));
+    if (extra) r.add_mixed(*extra);
+    typename G::Aff a = r.to_affine_low_latency();
+    const uint32_t inf = r.is_inf() ? 1u : 0u;
+    if (to_std) {
+        Fq* f = reinterpret_cast<Fq*>(&a);
+        for (int i = 0; i < (int)(sizeof(a) / sizeof(Fq)); ++i) f[i] = f[i].from_mont();
+    }
+    *out = a;
+    *reinterpret_cast<uint32_t*>(out + 1) = inf;
+}
+template <typename G>
+static void g_sum_strided_t(b200_ctx* ctx, const void* base, size_t stride, int n, const void* extra, void* out, bool to_std) {
+    g_sum_strided_kernel<G><<<1, 32, 0, ctx->cur()>>>((const unsigned char*)base, stride, n, (const typename G::Aff*)extra, (typename G::Aff*)out, to_std);
+    ctx->launches++;
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
 template <typename G>
 static void g_finish_t(b200_ctx* ctx, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {
     g_finish_kernel<G><<<1, 32, 0, ctx->cur()>>>((const typename G::Pt*)xt, nx, (const typename G::Aff*)at, na, (typename G::Aff*)out, to_std);
@@ -159,6 +184,9 @@ static void g_precompute_t(b200_ctx* ctx, const void* d_bases, size_t n, int c, 
     void g_precompute_##SUFFIX(b200_ctx* ctx, const void* b, size_t n, int c, void* t) { g_precompute_t<G>(ctx, b, n, c, t); }         \
     void g_finish_##SUFFIX(b200_ctx* ctx, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {                   \
         g_finish_t<G>(ctx, xt, nx, at, na, out, to_std);                                                                               \
+    }                                                                                                                                  \
+    void g_sum_strided_##SUFFIX(b200_ctx* ctx, const void* base, size_t stride, int n, const void* extra, void* out, bool to_std) {    \
+        g_sum_strided_t<G>(ctx, base, stride, n, extra, out, to_std);                                                                  \
     }                                                                                                                                  \
     void g_fixed_base_##SUFFIX(b200_ctx* ctx, const void* s, size_t n, void* out) { g_fixed_base_t<G>(ctx, s, n, out); }               \
     void g_add_affine_##SUFFIX(b200_ctx* ctx, const void* a, const void* b, void* out, size_t n) { g_add_affine_t<G>(ctx, a, b, out, n); } \

@@ -511,6 +511,36 @@ void spmv(b200_ctx* ctx, const DeviceCsr& M, const void* d_coeffs, const void* d
     B200_CUDA_CHECK(cudaGetLastError());
 }
 
+// Instanced rows (r1cs_constraint_light_instance + ITranslator, LS/relations/constraint_satisfaction_problems/r1cs/r1cs.hpp:145-211,
+// LS/relations/variable.hpp:279-314): n_inst instances of one master gadget share the master's rows; row j * n_master + r is
+// master row r evaluated through translation table j (tables[j * tlen + v] = the instance's index of master variable v;
+// index 0, the constant ONE, is never translated - variable.hpp:306-314).  HBM holds the master's CSR once and tlen u32 per
+// instance instead of the flattened rows (8 B per nonzero + 8 B per row, per instance, per matrix).
+__global__ void __launch_bounds__(128) spmv_instances_kernel(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col,
+                                                             const uint32_t* __restrict__ cidx, const Fr* __restrict__ coeffs,
+                                                             const Fr* __restrict__ w, const uint32_t* __restrict__ tables, uint32_t tlen,
+                                                             uint64_t n_master, uint64_t n_inst, Fr* __restrict__ out) {
+    const uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n_master * n_inst) return;
+    const uint64_t j = id / n_master, r = id - j * n_master;
+    const uint32_t* tab = tables + j * tlen;
+    Fr acc = Fr::zero();
+    for (uint64_t k = row_ptr[r], e = row_ptr[r + 1]; k < e; ++k) {
+        const uint32_t c = col[k];
+        acc = acc + coeffs[cidx[k]] * w[c ? tab[c] : 0u];
+    }
+    out[id] = acc;
+}
+void spmv_instances(b200_ctx* ctx, const DeviceCsr& master, const void* d_coeffs, const void* d_w, const uint32_t* d_tables, uint32_t tlen,
+                    uint64_t n_inst, void* d_out) {
+    const uint64_t n = master.n_rows * n_inst;
+    if (!n) return;
+    spmv_instances_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(master.row_ptr, master.col, master.cidx, (const Fr*)d_coeffs,
+                                                                                (const Fr*)d_w, d_tables, tlen, master.n_rows, n_inst, (Fr*)d_out);
+    ctx->launches++;
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
 // rows nc .. m-1 of the three evaluation vectors: input-consistency rows then zero padding (r1cs_to_qap.tcc:239-254)
 __global__ void witness_rows_kernel(const Fr* __restrict__ w, Fr* a, Fr* b, Fr* c, uint64_t nc, uint64_t ni, uint64_t m) {
     uint64_t i = nc + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -34,7 +34,8 @@ struct b200_key {
     void *A = nullptr, *B2 = nullptr, *B1 = nullptr, *H = nullptr, *L = nullptr;
     uint32_t *A_idx = nullptr, *B_idx = nullptr;
     uint32_t *A_pos = nullptr, *B_pos = nullptr;   // variable -> entry of the A / B query (0xffffffff = absent): shared digit list
-    bool A_ident = false, B_ident = false;         // the query's index list is 0, 1, 2, ...: no map needed
+    bool A_ident = false, B_ident = false;         // the query's index list is first, first + 1, first + 2, ...: no map needed
+    uint32_t A_first = 0, B_first = 0;             // (a whole dense key: first = 0; a shard of one: the start of its slice)
     // fixed-base window tables (built at circuit_load when ctx->precompute): [W][n] affine, window size per query
     void *A_t = nullptr, *B2_t = nullptr, *B1_t = nullptr, *H_t = nullptr, *L_t = nullptr;
     int cA = 0, cB = 0, cH = 0, cL = 0;
@@ -47,10 +48,19 @@ struct b200_key {
     uint64_t nc = 0, ni = 0, nv = 0, m = 0;
     uint32_t logm = 0;
     DeviceCsr M[3];
+    // instanced rows (b200_circuit_load_instanced): master gadget rows + one translation table per instance
+    DeviceCsr Mi[3];
+    uint32_t* inst_tables = nullptr;
+    uint32_t inst_tlen = 0;
+    uint64_t n_inst = 0, n_plain = 0;
     void* coeffs = nullptr;
     Domain dom;
     void *d_w = nullptr, *d_a = nullptr, *d_b = nullptr, *d_c = nullptr;
     uint64_t H_total = 0;       // |H_query| in the key file
+    // a key on a multi-device context: one shard per device (shards[i] on ctx->peers[i - 1], shards[0] on ctx); the
+    // wrapper itself holds no device memory
+    std::vector<b200_key*> shards;
+    void* gather = nullptr;     // on the first device: world x 256 B, the shards' affine partial sums (A 64 | B 128 | C 64)
 };
 
 namespace {
@@ -128,6 +138,18 @@ inline uint32_t bitrev32(uint32_t x, uint32_t bits) {
 
 void key_release(b200_key* k) {
     if (!k) return;
+    if (!k->shards.empty()) {
+        for (b200_key* sh : k->shards) {
+            if (!sh) continue;
+            cudaSetDevice(sh->ctx->device);
+            cudaStreamSynchronize(sh->ctx->stream);
+            key_release(sh);
+        }
+        cudaSetDevice(k->ctx->device);
+        cudaFree(k->gather);
+        delete k;
+        return;
+    }
     if (k->attached) {
         cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
         delete k;
@@ -137,7 +159,8 @@ void key_release(b200_key* k) {
     cudaFree(k->H);
     cudaFree(k->A_t); cudaFree(k->B2_t); cudaFree(k->B1_t); cudaFree(k->H_t); cudaFree(k->L_t);
     cudaFree(k->A_idx); cudaFree(k->B_idx); cudaFree(k->A_pos); cudaFree(k->B_pos); cudaFree(k->consts_g1); cudaFree(k->consts_g2);
-    for (int i = 0; i < 3; ++i) csr_free(&k->M[i]);
+    for (int i = 0; i < 3; ++i) { csr_free(&k->M[i]); csr_free(&k->Mi[i]); }
+    cudaFree(k->inst_tables);
     cudaFree(k->coeffs);
     if (k->has_circuit) domain_free(&k->dom);
     cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
@@ -183,31 +206,33 @@ __global__ void pos_scatter_kernel(const uint32_t* __restrict__ idx, uint32_t n,
     if (i < n && idx[i] < nvar) pos[idx[i]] = i;
 }
 // inverse of a query's variable index list, for the shared digit list of the witness MSMs (msm_common.cuh: MsmShared)
-__global__ void idx_not_identity_kernel(const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ flag) {
+__global__ void idx_not_contiguous_kernel(const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ flag) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n && idx[i] != i) *flag = 1u;
+    if (i < n && idx[i] != idx[0] + i) *flag = 1u;
 }
-void build_pos_map(b200_key* k, const uint32_t* idx, uint64_t n, uint32_t** pos, bool* ident) {
+void build_pos_map(b200_key* k, const uint32_t* idx, uint64_t n, uint32_t** pos, bool* ident, uint32_t* first) {
     cudaFree(*pos);
     *pos = nullptr;
     *ident = false;
+    *first = 0;
     const uint64_t nvar = k->nv + 1;
-    if (!idx || !n || k->world != 1 || nvar >= (1ull << B200_SHARED_VAR_BITS)) return;
+    if (!idx || !n || nvar >= (1ull << B200_SHARED_VAR_BITS)) return;
     B200_CUDA_CHECK(cudaMalloc(pos, nvar * 4));
     B200_CUDA_CHECK(cudaMemsetAsync(*pos, 0xff, nvar * 4, k->ctx->stream));
     pos_scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, k->ctx->stream>>>(idx, (uint32_t)n, *pos, (uint32_t)nvar);
     uint32_t* flag = (uint32_t*)k->ctx->scratch("pos_flag", 4);
     B200_CUDA_CHECK(cudaMemsetAsync(flag, 0, 4, k->ctx->stream));
-    idx_not_identity_kernel<<<(unsigned)((n + 255) / 256), 256, 0, k->ctx->stream>>>(idx, (uint32_t)n, flag);
+    idx_not_contiguous_kernel<<<(unsigned)((n + 255) / 256), 256, 0, k->ctx->stream>>>(idx, (uint32_t)n, flag);
     k->ctx->launches += 2;
     uint32_t h = 1;
     B200_CUDA_CHECK(cudaMemcpyAsync(&h, flag, 4, cudaMemcpyDeviceToHost, k->ctx->stream));
+    B200_CUDA_CHECK(cudaMemcpyAsync(first, idx, 4, cudaMemcpyDeviceToHost, k->ctx->stream));
     B200_CUDA_CHECK(cudaStreamSynchronize(k->ctx->stream));
     *ident = (h == 0);
 }
 void build_tables(b200_key* k) {
-    build_pos_map(k, k->A_idx, k->nA, &k->A_pos, &k->A_ident);
-    build_pos_map(k, k->B_idx, k->nB, &k->B_pos, &k->B_ident);
+    build_pos_map(k, k->A_idx, k->nA, &k->A_pos, &k->A_ident, &k->A_first);
+    build_pos_map(k, k->B_idx, k->nB, &k->B_pos, &k->B_ident, &k->B_first);
     build_table(k, 1, k->A, k->nA, &k->A_t, &k->cA);
     build_table(k, 2, k->B2, k->nB, &k->B2_t, &k->cB);
     if (k->full) { int cb1 = 0; build_table(k, 1, k->B1, k->nB, &k->B1_t, &cb1); if (cb1 != k->cB) { cudaFree(k->B1_t); k->B1_t = nullptr; } }
@@ -267,13 +292,63 @@ int key_load_cache(b200_ctx* ctx, const uint8_t* p, size_t len, int rank, int wo
     return (int)B200_OK;
 }
 
+// context of shard i of a multi-device context
+inline b200_ctx* shard_ctx(b200_ctx* root, int i) { return i == 0 ? root : root->peers[i - 1]; }
+inline int group_world(b200_ctx* root) { return 1 + (int)root->peers.size(); }
+// runs f(i) for every device of the context, device i on its own host thread (device 0 on the caller's)
+template <typename F>
+void for_each_device(b200_ctx* root, F&& f) {
+    const int world = group_world(root);
+    for (int i = 1; i < world; ++i) root->workers[i - 1]->start([&f, i] { f(i); });
+    std::exception_ptr err;
+    try { B200_CUDA_CHECK(cudaSetDevice(root->device)); f(0); } catch (...) { err = std::current_exception(); }
+    for (int i = 1; i < world; ++i) {
+        try { root->workers[i - 1]->wait(); } catch (...) { if (!err) err = std::current_exception(); }
+    }
+    cudaSetDevice(root->device);
+    if (err) std::rethrow_exception(err);
+}
+b200_key* new_group_key(b200_ctx* root) {
+    b200_key* g = new b200_key();
+    g->ctx = root;
+    g->world = group_world(root);
+    g->shards.assign(g->world, nullptr);
+    return g;
+}
+
 }  // namespace
 
 extern "C" {
 
+static int key_load_one(b200_ctx* ctx, const void* bytes, size_t len, int fmt, int rank, int world, b200_key** out);
+int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt, int rank, int world, b200_key** out);
+
+int b200_key_load(b200_ctx* ctx, const void* bytes, size_t len, int fmt, b200_key** out) {
+    if (!ctx || ctx->peers.empty()) return b200_key_load_sharded(ctx, bytes, len, fmt, 0, 1, out);
+    if (!bytes || !out) return B200_ERR_ARG;
+    *out = nullptr;
+    // multi-device context: every device parses the byte stream and keeps its 1/N slice of every query
+    return Guard{ctx}.run([&] {
+        std::unique_ptr<b200_key, void (*)(b200_key*)> g(new_group_key(ctx), key_release);
+        std::vector<int> rcs(g->world, 0);
+        for_each_device(ctx, [&](int i) { rcs[i] = key_load_one(shard_ctx(ctx, i), bytes, len, fmt, i, g->world, &g->shards[i]); });
+        for (int i = 0; i < g->world; ++i)
+            if (rcs[i]) { ctx->last_error = shard_ctx(ctx, i)->last_error; return rcs[i]; }
+        g->full = g->shards[0]->full; g->domain_size = g->shards[0]->domain_size; g->H_total = g->shards[0]->H_total;
+        for (b200_key* sh : g->shards) { g->nA += sh->nA; g->nB += sh->nB; g->nL += sh->nL; }
+        *out = g.release();
+        return (int)B200_OK;
+    });
+}
+
 int b200_key_load_sharded(b200_ctx* ctx, const void* bytes, size_t len, int fmt, int rank, int world, b200_key** out) {
     if (!ctx || !bytes || !out || fmt < 0 || fmt > 4 || world < 1 || rank < 0 || rank >= world) return B200_ERR_ARG;
     *out = nullptr;
+    if (!ctx->peers.empty() && world != 1) { ctx->last_error = "key_load_sharded on a multi-device context: it shards keys itself (b200_key_load)"; return B200_ERR_ARG; }
+    if (!ctx->peers.empty()) return b200_key_load(ctx, bytes, len, fmt, out);
+    return key_load_one(ctx, bytes, len, fmt, rank, world, out);
+}
+static int key_load_one(b200_ctx* ctx, const void* bytes, size_t len, int fmt, int rank, int world, b200_key** out) {
     if (fmt == B200_FMT_CACHE) return Guard{ctx}.run([&] { return key_load_cache(ctx, (const uint8_t*)bytes, len, rank, world, out); });
     return Guard{ctx}.run([&] {
         std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
@@ -407,16 +482,60 @@ int b200_key_export(b200_key* k, void* buf, size_t cap, size_t* len_out) {
     });
 }
 
-int b200_key_load(b200_ctx* ctx, const void* bytes, size_t len, int fmt, b200_key** out) {
-    return b200_key_load_sharded(ctx, bytes, len, fmt, 0, 1, out);
-}
-
 int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b200_bases* B_g2, b200_bases* B_g1, const uint32_t* B_idx,
                         b200_bases* H, b200_bases* L, const uint64_t* g1c, const uint64_t* g2c, uint64_t num_variables, uint64_t num_inputs,
                         b200_key** out) {
     if (!ctx || !A || !B_g2 || !H || !L || !g1c || !g2c || !out) return B200_ERR_ARG;
     if (A->group != 1 || B_g2->group != 2 || H->group != 1 || L->group != 1 || (B_g1 && (B_g1->group != 1 || B_g1->n != B_g2->n))) return B200_ERR_ARG;
     if (num_inputs > num_variables || L->n > num_variables - num_inputs) return B200_ERR_ARG;
+    if (!ctx->peers.empty()) {
+        // multi-device context: the base sets live on the first device; device i gets a COPY of its index range of A, B and L
+        // over peer memory (the shards own their copies, unlike the single-device key, which borrows the caller's sets)
+        return Guard{ctx}.run([&] {
+            std::unique_ptr<b200_key, void (*)(b200_key*)> g(new_group_key(ctx), key_release);
+            const int world = g->world;
+            std::vector<uint8_t> H_host(H->n * 64);
+            if (H->n) B200_CUDA_CHECK(cudaMemcpy(H_host.data(), H->d, H->n * 64, cudaMemcpyDeviceToHost));
+            B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+            for_each_device(ctx, [&](int i) {
+                b200_ctx* c = shard_ctx(ctx, i);
+                std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
+                k->ctx = c; k->owns_bases = true; k->full = B_g1 != nullptr; k->rank = i; k->world = world;
+                k->domain_size = num_variables + 1;
+                auto slice = [&](const b200_bases* b, size_t esz, uint64_t lo, uint64_t hi) {
+                    void* d = nullptr;
+                    B200_CUDA_CHECK(cudaMalloc(&d, std::max<size_t>((hi - lo) * esz, 16)));
+                    if (hi > lo) B200_CUDA_CHECK(cudaMemcpyPeer(d, c->device, (const char*)b->d + lo * esz, ctx->device, (hi - lo) * esz));
+                    return d;
+                };
+                auto idx_slice = [&](const uint32_t* idx, uint64_t lo, uint64_t hi) {
+                    std::vector<uint32_t> v(hi - lo);
+                    for (uint64_t j = lo; j < hi; ++j) {
+                        v[j - lo] = idx ? idx[j] : (uint32_t)j;
+                        if (v[j - lo] > num_variables) throw std::invalid_argument("key_from_bases: query index beyond num_variables");
+                    }
+                    return dev_upload(v);
+                };
+                uint64_t lo, hi;
+                shard_range(A->n, i, world, lo, hi);
+                k->A = slice(A, 64, lo, hi); k->nA = hi - lo; k->A_idx = idx_slice(A_idx, lo, hi);
+                shard_range(B_g2->n, i, world, lo, hi);
+                k->B2 = slice(B_g2, 128, lo, hi); k->nB = hi - lo; k->B_idx = idx_slice(B_idx, lo, hi);
+                if (B_g1) k->B1 = slice(B_g1, 64, lo, hi);
+                shard_range(L->n, i, world, lo, hi);
+                k->L = slice(L, 64, lo, hi); k->nL = hi - lo; k->L_lo = lo;
+                k->consts_g1 = dev_upload_bytes((const uint8_t*)g1c, 3 * 64);
+                k->consts_g2 = dev_upload_bytes((const uint8_t*)g2c, 2 * 128);
+                k->H_total = H->n;
+                k->H_host = H_host;
+                g->shards[i] = k.release();
+            });
+            g->full = B_g1 != nullptr; g->domain_size = num_variables + 1; g->H_total = H->n;
+            g->nA = A->n; g->nB = B_g2->n; g->nL = L->n;
+            *out = g.release();
+            return (int)B200_OK;
+        });
+    }
     return Guard{ctx}.run([&] {
         std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(), key_release);
         k->ctx = ctx; k->owns_bases = false; k->full = B_g1 != nullptr;
@@ -444,13 +563,14 @@ int b200_key_from_bases(b200_ctx* ctx, b200_bases* A, const uint32_t* A_idx, b20
 }
 
 int b200_key_set_shard(b200_key* k, int rank, int world, uint64_t L_lo) {
-    if (!k || world < 1 || rank < 0 || rank >= world || k->has_circuit) return B200_ERR_ARG;
+    if (!k || world < 1 || rank < 0 || rank >= world || k->has_circuit || !k->shards.empty()) return B200_ERR_ARG;
     k->rank = rank; k->world = world; k->L_lo = L_lo;
     return B200_OK;
 }
 
 int b200_key_attach(b200_key* key, b200_ctx* ctx, b200_key** out) {
     if (!key || !ctx || !out) return B200_ERR_ARG;
+    if (!key->shards.empty()) { ctx->last_error = "key_attach: not for keys on a multi-device context"; return B200_ERR_STATE; }
     if (!key->has_circuit) { ctx->last_error = "key_attach before circuit_load"; return B200_ERR_STATE; }
     if (ctx->device != key->ctx->device) { ctx->last_error = "key_attach: the context is on another device"; return B200_ERR_ARG; }
     return Guard{ctx}.run([&] {
@@ -479,17 +599,43 @@ void b200_key_free(b200_key* key) {
 }
 int b200_key_info(b200_key* k, uint64_t out[8]) {
     if (!k || !out) return B200_ERR_ARG;
+    if (!k->shards.empty() && k->has_circuit) { k->nH = 0; for (b200_key* sh : k->shards) k->nH += sh->nH; k->H_bitrev = true; }
     out[0] = k->domain_size; out[1] = k->nA; out[2] = k->nB; out[3] = k->H_bitrev ? k->nH : k->H_total; out[4] = k->nL;
     out[5] = k->full; out[6] = k->m; out[7] = k->ni;
     return B200_OK;
 }
 
+static int circuit_load_impl(b200_key* k, const b200_csr* A, const b200_csr* B, const b200_csr* C, const b200_instances* inst,
+                             const uint64_t* coeffs, size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables);
 int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b200_csr* C, const uint64_t* coeffs, size_t n_coeffs,
                       uint32_t num_inputs, uint64_t num_variables) {
+    return circuit_load_impl(k, A, B, C, nullptr, coeffs, n_coeffs, num_inputs, num_variables);
+}
+int b200_circuit_load_instanced(b200_key* k, const b200_csr* A, const b200_csr* B, const b200_csr* C, const b200_instances* inst,
+                                const uint64_t* coeffs, size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables) {
+    if (!inst || !inst->A || !inst->B || !inst->C || (inst->n_instances && !inst->tables) || !inst->table_len) return B200_ERR_ARG;
+    if (inst->A->n_rows != inst->B->n_rows || inst->A->n_rows != inst->C->n_rows) return B200_ERR_ARG;
+    return circuit_load_impl(k, A, B, C, inst, coeffs, n_coeffs, num_inputs, num_variables);
+}
+static int circuit_load_impl(b200_key* k, const b200_csr* A, const b200_csr* B, const b200_csr* C, const b200_instances* inst,
+                             const uint64_t* coeffs, size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables) {
     if (!k || !A || !B || !C || !coeffs || !n_coeffs) return B200_ERR_ARG;
     if (A->n_rows != B->n_rows || A->n_rows != C->n_rows) return B200_ERR_ARG;
     if (num_variables + 1 != k->domain_size || num_inputs > num_variables) return B200_ERR_ARG;
     b200_ctx* ctx = k->ctx;
+    if (!k->shards.empty()) {
+        // multi-device key: every device holds the whole circuit (the witness map is small) and its slice of the queries
+        return Guard{ctx}.run([&] {
+            std::vector<int> rcs(k->world, 0);
+            for_each_device(ctx, [&](int i) { rcs[i] = circuit_load_impl(k->shards[i], A, B, C, inst, coeffs, n_coeffs, num_inputs, num_variables); });
+            for (int i = 0; i < k->world; ++i)
+                if (rcs[i]) { ctx->last_error = shard_ctx(ctx, i)->last_error; return rcs[i]; }
+            if (!k->gather) B200_CUDA_CHECK(cudaMalloc(&k->gather, (size_t)k->world * 256 + 1024));
+            k->has_circuit = true;
+            k->nc = k->shards[0]->nc; k->ni = num_inputs; k->nv = num_variables; k->m = k->shards[0]->m; k->logm = k->shards[0]->logm;
+            return (int)B200_OK;
+        });
+    }
     return Guard{ctx}.run([&] {
         const b200_csr* mats[3] = {A, B, C};
         for (int i = 0; i < 3; ++i) {
@@ -499,15 +645,30 @@ int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b
                 if (mats[i]->coeff_idx[j] >= n_coeffs) throw std::invalid_argument("circuit_load: coefficient index out of range");
             }
         }
+        if (inst) {
+            const b200_csr* im[3] = {inst->A, inst->B, inst->C};
+            for (int i = 0; i < 3; ++i) {
+                const uint64_t nnz = im[i]->n_rows ? im[i]->row_ptr[im[i]->n_rows] : 0;
+                for (uint64_t j = 0; j < nnz; ++j) {
+                    if (im[i]->col[j] >= inst->table_len) throw std::invalid_argument("circuit_load_instanced: master variable index beyond table_len");
+                    if (im[i]->coeff_idx[j] >= n_coeffs) throw std::invalid_argument("circuit_load_instanced: coefficient index out of range");
+                }
+            }
+            const uint64_t nt = inst->n_instances * (uint64_t)inst->table_len;
+            for (uint64_t j = 0; j < nt; ++j)
+                if (inst->tables[j] > num_variables) throw std::invalid_argument("circuit_load_instanced: translated variable index out of range");
+        }
         if (k->has_circuit) {
-            for (int i = 0; i < 3; ++i) csr_free(&k->M[i]);
+            for (int i = 0; i < 3; ++i) { csr_free(&k->M[i]); csr_free(&k->Mi[i]); }
+            cudaFree(k->inst_tables); k->inst_tables = nullptr; k->n_inst = 0; k->inst_tlen = 0;
             cudaFree(k->coeffs); k->coeffs = nullptr;
             domain_free(&k->dom);
             cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
             k->d_w = k->d_a = k->d_b = k->d_c = nullptr;
             k->has_circuit = false;
         }
-        k->nc = A->n_rows; k->ni = num_inputs; k->nv = num_variables;
+        k->n_plain = A->n_rows;
+        k->nc = A->n_rows + (inst ? inst->n_instances * inst->A->n_rows : 0); k->ni = num_inputs; k->nv = num_variables;
         // get_domain (src/stubs.cpp:61-75): m = roundUpToNearestPowerOf2(num_constraints + num_inputs + 1)
         uint64_t need = k->nc + k->ni + 1;
         uint32_t logm = 0;
@@ -520,6 +681,12 @@ int b200_circuit_load(b200_key* k, const b200_csr* A, const b200_csr* B, const b
         if (k->world == 1 && k->nL != k->nv - k->ni) throw std::invalid_argument("circuit_load: L query length differs from num_variables - num_inputs");
         if (k->nA > k->nv + 1 || k->nB > k->nv + 1) throw std::invalid_argument("circuit_load: A or B query longer than num_variables + 1");
         for (int i = 0; i < 3; ++i) csr_upload(ctx, mats[i]->row_ptr, mats[i]->col, mats[i]->coeff_idx, mats[i]->n_rows, &k->M[i]);
+        if (inst) {
+            const b200_csr* im[3] = {inst->A, inst->B, inst->C};
+            for (int i = 0; i < 3; ++i) csr_upload(ctx, im[i]->row_ptr, im[i]->col, im[i]->coeff_idx, im[i]->n_rows, &k->Mi[i]);
+            k->inst_tables = (uint32_t*)dev_upload_bytes((const uint8_t*)inst->tables, inst->n_instances * (size_t)inst->table_len * 4);
+            k->inst_tlen = inst->table_len; k->n_inst = inst->n_instances;
+        }
         k->coeffs = dev_upload_bytes((const uint8_t*)coeffs, n_coeffs * 32);
         domain_create(ctx, logm, &k->dom);
         k->has_circuit = true;
@@ -653,13 +820,15 @@ namespace {
 void run_witness_eval(b200_key* k, const uint64_t* witness) {
     b200_ctx* ctx = k->ctx;
     ctx->t_begin("h2d.witness");
-    B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
+    if (witness) B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
     B200_CUDA_CHECK(cudaEventRecord(ctx->ev_witness, ctx->stream));
     ctx->t_end();
     ctx->t_begin("witness_eval");
-    spmv(ctx, k->M[0], k->coeffs, k->d_w, k->d_a);
-    spmv(ctx, k->M[1], k->coeffs, k->d_w, k->d_b);
-    spmv(ctx, k->M[2], k->coeffs, k->d_w, k->d_c);
+    void* outs[3] = {k->d_a, k->d_b, k->d_c};
+    for (int i = 0; i < 3; ++i) {
+        spmv(ctx, k->M[i], k->coeffs, k->d_w, outs[i]);
+        if (k->n_inst) spmv_instances(ctx, k->Mi[i], k->coeffs, k->d_w, k->inst_tables, k->inst_tlen, k->n_inst, (char*)outs[i] + k->n_plain * 32);
+    }
     witness_rows(ctx, k->d_w, k->d_a, k->d_b, k->d_c, k->nc, k->ni, k->m);
     ctx->t_end();
 }
@@ -697,32 +866,42 @@ void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1, int finish =
     };
     // One sorted digit list for all of them when every query is dense over the variables and the tables share a window
     // size: digits + sort + offsets run once (on the G2 lane) instead of three or four times.
-    const uint64_t nvar = k->nv + 1;
-    const bool share = ctx->shared_sort && ctx->affine_rounds == 0 && k->world == 1 && k->A_t && k->B2_t && k->L_t && k->A_pos && k->B_pos &&
-                       k->cA == k->cB && k->cA == k->cL && k->cA >= 8 /* <= 32 windows */ && (!want_b1 || k->B1_t) && nvar < (1ull << B200_SHARED_VAR_BITS) &&
-                       5 * k->nA >= 4 * nvar && 5 * k->nB >= 4 * nvar && 5 * k->nL >= 4 * nvar;
+    // The list covers the variable range [v0, v1) the queries of this key (or of this rank's shard of it) touch; a query is
+    // addressed through its variable -> entry map, or through an index range when its index list is contiguous.
+    uint64_t v0 = 0, v1 = k->nv + 1;
+    if (k->world != 1 && k->A_ident && k->B_ident && k->nA && k->nB && k->nL) {
+        const uint64_t l0 = k->ni + 1 + k->L_lo;
+        v0 = std::min<uint64_t>(std::min<uint64_t>(k->A_first, k->B_first), l0);
+        v1 = std::max<uint64_t>(std::max<uint64_t>(k->A_first + k->nA, k->B_first + k->nB), l0 + k->nL);
+    }
+    const uint64_t nvar = v1 - v0;
+    const bool share = ctx->shared_sort && ctx->affine_rounds == 0 && (k->world == 1 || (k->A_ident && k->B_ident)) && k->A_t && k->B2_t && k->L_t &&
+                       k->A_pos && k->B_pos && k->cA == k->cB && k->cA == k->cL && k->cA >= 8 /* <= 32 windows */ && (!want_b1 || k->B1_t) &&
+                       k->nv + 1 < (1ull << B200_SHARED_VAR_BITS) && 5 * k->nA >= 4 * nvar && 5 * k->nB >= 4 * nvar && 5 * k->nL >= 4 * nvar;
     if (share) {
         try {
             MsmShared sh;
             lane_begin(1, "msm.B_g2");
             ctx->t_begin("msm.shared_sort");
-            msm_shared_prepare(ctx, k->d_w, nvar, k->cA, &sh);
+            msm_shared_prepare(ctx, (const char*)k->d_w + v0 * 32, nvar, k->cA, &sh);
             ctx->t_end();
             if (ctx->lane) B200_CUDA_CHECK(cudaEventRecord(ctx->ev_shared, ctx->lanes[ctx->lane]));
-            msm_shared_consume_g2(ctx, sh, k->B2_t, MsmPos{k->B_ident ? nullptr : k->B_pos, 0, (uint32_t)k->nB, (uint32_t)k->nB}, a.B2);
+            const MsmPos posA{k->A_ident ? nullptr : k->A_pos + v0, (uint32_t)(k->A_first - v0), (uint32_t)k->nA, (uint32_t)k->nA};
+            const MsmPos posB{k->B_ident ? nullptr : k->B_pos + v0, (uint32_t)(k->B_first - v0), (uint32_t)k->nB, (uint32_t)k->nB};
+            msm_shared_consume_g2(ctx, sh, k->B2_t, posB, a.B2);
             if (finish == 1) g_finish(ctx, 2, a.B2, 1, k->consts_g2, 1, fin + 256, true);
             if (finish == 2) g_finish(ctx, 2, a.B2, 1, nullptr, 0, fin + 256, false);
             lane_end();
             lane_begin(2, "msm.A");
             if (ctx->lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->lanes[ctx->lane], ctx->ev_shared, 0));
-            msm_shared_consume_g1(ctx, sh, k->A_t, MsmPos{k->A_ident ? nullptr : k->A_pos, 0, (uint32_t)k->nA, (uint32_t)k->nA}, a.A);
-            if (want_b1) msm_shared_consume_g1(ctx, sh, k->B1_t, MsmPos{k->B_ident ? nullptr : k->B_pos, 0, (uint32_t)k->nB, (uint32_t)k->nB}, a.B1);
+            msm_shared_consume_g1(ctx, sh, k->A_t, posA, a.A);
+            if (want_b1) msm_shared_consume_g1(ctx, sh, k->B1_t, posB, a.B1);
             if (finish == 1) g_finish(ctx, 1, a.A, 1, k->consts_g1, 1, fin, true);
             if (finish == 2) g_finish(ctx, 1, a.A, 1, nullptr, 0, fin, false);
             lane_end();
             lane_begin(3, "msm.L");
             if (ctx->lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->lanes[ctx->lane], ctx->ev_shared, 0));
-            msm_shared_consume_g1(ctx, sh, k->L_t, MsmPos{nullptr, (uint32_t)(k->ni + 1 + k->L_lo), (uint32_t)k->nL, (uint32_t)k->nL}, a.L);
+            msm_shared_consume_g1(ctx, sh, k->L_t, MsmPos{nullptr, (uint32_t)(k->ni + 1 + k->L_lo - v0), (uint32_t)k->nL, (uint32_t)k->nL}, a.L);
             lane_end();
         } catch (...) { ctx->lane = 0; throw; }
         return;
@@ -752,15 +931,46 @@ void run_msm_h_and_join(b200_key* k, const Acc& a) {
     if (ctx->overlap)
         for (int lane = 1; lane < 4; ++lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->lane_done[lane], 0));
 }
-void fetch(b200_ctx* ctx, int group, const void* d_fin, uint64_t* xy, uint8_t* inf) {
-    uint8_t buf[128 + 16];
-    const size_t ab = group == 1 ? 64 : 128;
-    B200_CUDA_CHECK(cudaMemcpyAsync(buf, d_fin, ab + 4, cudaMemcpyDeviceToHost, ctx->stream));
+// the three finished points sit 256 B apart in one scratch block (A at 0, B at 256, C at 512, each followed by its u32
+// infinity flag): one copy, one synchronisation
+void fetch3(b200_ctx* ctx, const void* d_fin, uint64_t* A_xy, uint64_t* B_xy, uint64_t* C_xy, uint8_t* flags) {
+    uint8_t buf[768];
+    B200_CUDA_CHECK(cudaMemcpyAsync(buf, d_fin, 512 + 64 + 4, cudaMemcpyDeviceToHost, ctx->stream));
     B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
-    memcpy(xy, buf, ab);
     uint32_t f;
-    memcpy(&f, buf + ab, 4);
-    *inf = (uint8_t)(f != 0);
+    memcpy(A_xy, buf, 64);        memcpy(&f, buf + 64, 4);        flags[0] = (uint8_t)(f != 0);
+    memcpy(B_xy, buf + 256, 128); memcpy(&f, buf + 256 + 128, 4); flags[1] = (uint8_t)(f != 0);
+    memcpy(C_xy, buf + 512, 64);  memcpy(&f, buf + 512 + 64, 4);  flags[2] = (uint8_t)(f != 0);
+}
+// queues one rank's partial proof: on return (no synchronisation) the three affine Montgomery partial sums are being written
+// to fin + 0 / + 256 / + 512 of the context's scratch.  witness == nullptr: the witness is already in k->d_w.
+char* partial_async(b200_key* k, const uint64_t* witness) {
+    b200_ctx* ctx = k->ctx;
+    ctx->t_begin("prove.total");
+    Acc a = acc_slots(ctx);
+    run_witness_eval(k, witness);
+    run_msms_witness_only(k, a, false, 2);
+    run_h(k);
+    run_msm_h_and_join(k, a);
+    char* fin = (char*)a.fin;
+    g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, false);
+    ctx->t_end();
+    return fin;
+}
+// A 64 B | B 128 B | C 64 B (the point at infinity is (0,0)) to dst, which may be on another device (peer memory)
+void pack_partial(b200_ctx* ctx, const char* fin, void* dst) {
+    B200_CUDA_CHECK(cudaMemcpyAsync(dst, fin, 64, cudaMemcpyDefault, ctx->stream));
+    B200_CUDA_CHECK(cudaMemcpyAsync((char*)dst + 64, fin + 256, 128, cudaMemcpyDefault, ctx->stream));
+    B200_CUDA_CHECK(cudaMemcpyAsync((char*)dst + 192, fin + 512, 64, cudaMemcpyDefault, ctx->stream));
+}
+// sums `world` packed partials (device memory of ctx's device), adds alpha_g1 / beta_g2, leaves the proof in fin (standard form)
+char* combine_async(b200_key* k, const void* d_parts, int world) {
+    b200_ctx* ctx = k->ctx;
+    char* fin = (char*)acc_slots(ctx).fin + 2048;
+    g_sum_strided(ctx, 1, d_parts, 256, world, k->consts_g1, fin, true);
+    g_sum_strided(ctx, 2, (const char*)d_parts + 64, 256, world, k->consts_g2, fin + 256, true);
+    g_sum_strided(ctx, 1, (const char*)d_parts + 192, 256, world, nullptr, fin + 512, true);
+    return fin;
 }
 
 }  // namespace
@@ -770,6 +980,7 @@ extern "C" {
 int b200_witness_eval(b200_key* k, const uint64_t* witness, uint64_t* a_out, uint64_t* b_out, uint64_t* c_out) {
     if (!k || !witness || !a_out || !b_out || !c_out) return B200_ERR_ARG;
     if (!k->has_circuit) { k->ctx->last_error = "witness_eval before circuit_load"; return B200_ERR_STATE; }
+    if (!k->shards.empty()) return b200_witness_eval(k->shards[0], witness, a_out, b_out, c_out);
     b200_ctx* ctx = k->ctx;
     return Guard{ctx}.run([&] {
         run_witness_eval(k, witness);
@@ -785,6 +996,7 @@ int b200_witness_eval(b200_key* k, const uint64_t* witness, uint64_t* a_out, uin
 int b200_h(b200_key* k, const uint64_t* witness, uint64_t* h_out) {
     if (!k || !witness || !h_out) return B200_ERR_ARG;
     if (!k->has_circuit) { k->ctx->last_error = "h before circuit_load"; return B200_ERR_STATE; }
+    if (!k->shards.empty()) return b200_h(k->shards[0], witness, h_out);
     b200_ctx* ctx = k->ctx;
     return Guard{ctx}.run([&] {
         run_witness_eval(k, witness);
@@ -802,6 +1014,35 @@ int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const 
     if (!k || !witness || !A_xy || !B_xy || !C_xy || !flags || ((r == nullptr) != (s == nullptr))) return B200_ERR_ARG;
     b200_ctx* ctx = k->ctx;
     if (!k->has_circuit) { ctx->last_error = "prove before circuit_load"; return B200_ERR_STATE; }
+    if (!k->shards.empty()) {
+        if (r) { ctx->last_error = "r,s proving is not available on a multi-device context"; return B200_ERR_STATE; }
+        // One proof on all devices of the context.  The witness goes to the first device once; every other device pulls it
+        // over peer memory, runs the whole pipeline on its 1/N slice of the queries (its launch sequence issued by its own
+        // host thread) and pushes its three affine partial sums into the first device's gather buffer; the first device adds
+        // them and alpha_g1 / beta_g2.  No host round trip between the witness upload and the proof download.
+        return Guard{ctx}.run([&] {
+            b200_key* k0 = k->shards[0];
+            B200_CUDA_CHECK(cudaMemcpyAsync(k0->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
+            cudaEvent_t ev_w = ctx->ev_group;
+            B200_CUDA_CHECK(cudaEventRecord(ev_w, ctx->stream));
+            for_each_device(ctx, [&](int i) {
+                b200_key* ki = k->shards[i];
+                b200_ctx* ci = ki->ctx;
+                if (i) B200_CUDA_CHECK(cudaStreamWaitEvent(ci->stream, ev_w, 0));
+                char* fin = partial_async(ki, i ? (const uint64_t*)k0->d_w : nullptr);
+                pack_partial(ci, fin, (char*)k->gather + (size_t)i * 256);
+                if (i) B200_CUDA_CHECK(cudaEventRecord(ci->ev_group, ci->stream));
+            });
+            for (int i = 1; i < k->world; ++i) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, k->shards[i]->ctx->ev_group, 0));
+            ctx->t_begin("combine");
+            char* fin = combine_async(k0, k->gather, k->world);
+            ctx->t_end();
+            fetch3(ctx, fin, A_xy, B_xy, C_xy, flags);
+            for (int i = 0; i < k->world; ++i) { cudaSetDevice(k->shards[i]->ctx->device); k->shards[i]->ctx->t_collect(); }
+            cudaSetDevice(ctx->device);
+            return (int)B200_OK;
+        });
+    }
     if (k->world != 1) { ctx->last_error = "prove on a sharded key: use prove_partial + proof_combine"; return B200_ERR_STATE; }
     if (r && !k->full) { ctx->last_error = "r,s proving needs a FULL key (B query in G1)"; return B200_ERR_STATE; }
     return Guard{ctx}.run([&] {
@@ -849,9 +1090,7 @@ int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const 
         }
         ctx->t_end();
         ctx->t_end();   // prove.total
-        fetch(ctx, 1, fin, A_xy, &flags[0]);
-        fetch(ctx, 2, fin + 256, B_xy, &flags[1]);
-        fetch(ctx, 1, fin + 512, C_xy, &flags[2]);
+        fetch3(ctx, fin, A_xy, B_xy, C_xy, flags);
         ctx->t_collect();
         return (int)B200_OK;
     });
@@ -861,19 +1100,39 @@ int b200_prove_partial(b200_key* k, const uint64_t* witness, uint64_t partial[32
     if (!k || !witness || !partial || !flags) return B200_ERR_ARG;
     b200_ctx* ctx = k->ctx;
     if (!k->has_circuit) { ctx->last_error = "prove_partial before circuit_load"; return B200_ERR_STATE; }
+    if (!k->shards.empty()) { ctx->last_error = "prove_partial on a multi-device context: b200_prove runs all devices"; return B200_ERR_STATE; }
     return Guard{ctx}.run([&] {
-        ctx->t_begin("prove.total");
-        Acc a = acc_slots(ctx);
-        run_witness_eval(k, witness);
-        run_msms_witness_only(k, a, false, 2);
-        run_h(k);
-        run_msm_h_and_join(k, a);
-        char* fin = (char*)a.fin;
-        g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, false);
+        char* fin = partial_async(k, witness);
+        fetch3(ctx, fin, partial, partial + 8, partial + 24, flags);
+        ctx->t_collect();
+        return (int)B200_OK;
+    });
+}
+
+// The same with the result left on the device: 256 bytes at d_out (A 64 | B 128 | C 64, affine Montgomery, (0,0) = infinity),
+// queued on b200_stream(ctx) WITHOUT synchronising, so that a collective on the same stream (ncclAllGather) can follow.
+int b200_prove_partial_dev(b200_key* k, const uint64_t* witness, void* d_out) {
+    if (!k || !witness || !d_out) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (!k->has_circuit) { ctx->last_error = "prove_partial before circuit_load"; return B200_ERR_STATE; }
+    if (!k->shards.empty()) { ctx->last_error = "prove_partial on a multi-device context: b200_prove runs all devices"; return B200_ERR_STATE; }
+    return Guard{ctx}.run([&] {
+        char* fin = partial_async(k, witness);
+        pack_partial(ctx, fin, d_out);
+        return (int)B200_OK;
+    });
+}
+// combines `world` packed partials that are already on this device (the all-gathered buffer) into the proof: three small
+// kernels on b200_stream(ctx), one copy back
+int b200_proof_combine_dev(b200_key* k, const void* d_parts, int world, uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t flags[3]) {
+    if (!k || !d_parts || world < 1 || !A_xy || !B_xy || !C_xy || !flags) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (!k->shards.empty()) return B200_ERR_STATE;
+    return Guard{ctx}.run([&] {
+        ctx->t_begin("combine");
+        char* fin = combine_async(k, d_parts, world);
         ctx->t_end();
-        fetch(ctx, 1, fin, partial, &flags[0]);
-        fetch(ctx, 2, fin + 256, partial + 8, &flags[1]);
-        fetch(ctx, 1, fin + 512, partial + 24, &flags[2]);
+        fetch3(ctx, fin, A_xy, B_xy, C_xy, flags);
         ctx->t_collect();
         return (int)B200_OK;
     });
@@ -892,19 +1151,19 @@ int b200_proof_combine(b200_key* k, const uint64_t* partials, const uint8_t* pfl
             if (!pflags[i * 3 + 2]) memcpy(&c1[(size_t)i * 64], p + 24, 64);
         }
         char* buf = (char*)ctx->scratch("combine", (size_t)(world + 1) * 256 + 1024);
-        char* fin = buf + (size_t)(world + 1) * 256;
+        char* fin = buf + (size_t)(world + 1) * 256;      // A terms | B terms | C terms | fin (3 x 256 B)
         // alpha_g1 / beta_g2 are appended as one more affine term
         B200_CUDA_CHECK(cudaMemcpyAsync(buf, a1.data(), (size_t)world * 64, cudaMemcpyHostToDevice, ctx->stream));
         B200_CUDA_CHECK(cudaMemcpyAsync(buf + (size_t)world * 64, k->consts_g1, 64, cudaMemcpyDeviceToDevice, ctx->stream));
         g_finish(ctx, 1, nullptr, 0, buf, world + 1, fin, true);
-        fetch(ctx, 1, fin, A_xy, &flags[0]);
-        B200_CUDA_CHECK(cudaMemcpyAsync(buf, b2.data(), (size_t)world * 128, cudaMemcpyHostToDevice, ctx->stream));
-        B200_CUDA_CHECK(cudaMemcpyAsync(buf + (size_t)world * 128, k->consts_g2, 128, cudaMemcpyDeviceToDevice, ctx->stream));
-        g_finish(ctx, 2, nullptr, 0, buf, world + 1, fin, true);
-        fetch(ctx, 2, fin, B_xy, &flags[1]);
-        B200_CUDA_CHECK(cudaMemcpyAsync(buf, c1.data(), (size_t)world * 64, cudaMemcpyHostToDevice, ctx->stream));
-        g_finish(ctx, 1, nullptr, 0, buf, world, fin, true);
-        fetch(ctx, 1, fin, C_xy, &flags[2]);
+        char* bufB = buf + (size_t)(world + 1) * 64;
+        B200_CUDA_CHECK(cudaMemcpyAsync(bufB, b2.data(), (size_t)world * 128, cudaMemcpyHostToDevice, ctx->stream));
+        B200_CUDA_CHECK(cudaMemcpyAsync(bufB + (size_t)world * 128, k->consts_g2, 128, cudaMemcpyDeviceToDevice, ctx->stream));
+        g_finish(ctx, 2, nullptr, 0, bufB, world + 1, fin + 256, true);
+        char* bufC = bufB + (size_t)(world + 1) * 128;
+        B200_CUDA_CHECK(cudaMemcpyAsync(bufC, c1.data(), (size_t)world * 64, cudaMemcpyHostToDevice, ctx->stream));
+        g_finish(ctx, 1, nullptr, 0, bufC, world, fin + 512, true);
+        fetch3(ctx, fin, A_xy, B_xy, C_xy, flags);
         return (int)B200_OK;
     });
 }

@@ -28,12 +28,17 @@ SYMBOLS = [
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
     "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
-    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc",
+    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc", "b200_device_count", "b200_circuit_load_instanced", "b200_prove_partial_dev", "b200_proof_combine_dev",
 ]
 
 
 class CSR(C.Structure):
     _fields_ = [("row_ptr", u64p), ("col", u32p), ("coeff_idx", u32p), ("n_rows", C.c_uint64)]
+
+
+class INSTANCES(C.Structure):
+    _fields_ = [("A", C.POINTER(CSR)), ("B", C.POINTER(CSR)), ("C", C.POINTER(CSR)), ("tables", u32p), ("table_len", C.c_uint32),
+                ("n_instances", C.c_uint64)]
 
 
 class B200Error(RuntimeError):
@@ -70,16 +75,19 @@ def _arr(a, dtype=np.uint64):
 
 
 class Context:
-    """One CUDA device, one stream (b200_init)."""
+    """One CUDA device, one stream (b200_init) - or, with a list of devices, ONE context spanning several GPUs of the box:
+    keys loaded on it are split 1/N per device and prove() runs on all of them from this process."""
 
     def __init__(self, device=0):
         self.lib = load()
         self.h = C.c_void_p()
-        dev = (C.c_int * 1)(device)
-        rc = self.lib.b200_init(dev, 1, C.byref(self.h))
+        devices = list(device) if isinstance(device, (list, tuple)) else [device]
+        dev = (C.c_int * len(devices))(*devices)
+        rc = self.lib.b200_init(dev, len(devices), C.byref(self.h))
         if rc:
-            raise B200Error(f"b200_init(device={device}) failed: {self.lib.b200_strerror(rc).decode()}")
-        self.device = device
+            raise B200Error(f"b200_init(devices={devices}) failed: {self.lib.b200_strerror(rc).decode()}")
+        self.device = devices[0]
+        self.devices = devices
         self._children = weakref.WeakSet()    # live Bases / ProvingKey objects: freed before the context goes away
 
     def check(self, rc, what):
@@ -368,6 +376,21 @@ class ProvingKey:
         self.num_inputs, self.num_variables = num_inputs, num_variables
         self.m = self.info()["m"]
 
+    def load_circuit_instanced(self, A, B, Cm, master, tables, coeffs_mont, num_inputs, num_variables):
+        """b200_circuit_load_instanced: plain rows A, B, Cm, then for every row j of `tables` (n_instances x table_len uint32) all
+        rows of `master` = (mA, mB, mC) translated through it.  The device keeps the master rows and the tables."""
+        keep, structs = _csr_structs((A, B, Cm))
+        mkeep, mstructs = _csr_structs(master)
+        tab = np.ascontiguousarray(tables, dtype=np.uint32).reshape(len(tables), -1)
+        inst = INSTANCES(C.pointer(mstructs[0]), C.pointer(mstructs[1]), C.pointer(mstructs[2]), tab.ctypes.data_as(u32p),
+                         C.c_uint32(tab.shape[1]), C.c_uint64(tab.shape[0]))
+        co = _arr(coeffs_mont)
+        self.ctx.check(self.ctx.lib.b200_circuit_load_instanced(self.h, C.byref(structs[0]), C.byref(structs[1]), C.byref(structs[2]),
+                                                                C.byref(inst), _p64(co), C.c_size_t(co.size // 4), C.c_uint32(num_inputs),
+                                                                C.c_uint64(num_variables)), "circuit_load_instanced")
+        self.num_inputs, self.num_variables = num_inputs, num_variables
+        self.m = self.info()["m"]
+
     def _wptr(self, witness):
         if isinstance(witness, int):
             return C.cast(C.c_void_p(witness), u64p), None
@@ -401,6 +424,19 @@ class ProvingKey:
         part = np.zeros(32, np.uint64); flags = np.zeros(3, np.uint8)
         self.ctx.check(self.ctx.lib.b200_prove_partial(self.h, wp, _p64(part), flags.ctypes.data_as(u8p)), "prove_partial")
         return part, flags
+
+    def prove_partial_dev(self, witness, d_out_ptr):
+        """b200_prove_partial_dev: this rank's 256-byte packed partial sums written to DEVICE memory at d_out_ptr, queued on the
+        context's stream without synchronising"""
+        wp, keep = self._wptr(witness)
+        self.ctx.check(self.ctx.lib.b200_prove_partial_dev(self.h, wp, C.c_void_p(d_out_ptr)), "prove_partial_dev")
+
+    def combine_dev(self, d_parts_ptr, world):
+        """b200_proof_combine_dev: `world` packed partials already on this device -> the proof (standard form)"""
+        A = np.zeros(8, np.uint64); B = np.zeros(16, np.uint64); Cc = np.zeros(8, np.uint64); inf = np.zeros(3, np.uint8)
+        self.ctx.check(self.ctx.lib.b200_proof_combine_dev(self.h, C.c_void_p(d_parts_ptr), world, _p64(A), _p64(B), _p64(Cc),
+                                                           inf.ctypes.data_as(u8p)), "proof_combine_dev")
+        return A, B, Cc, inf
 
     def combine(self, partials, flags):
         partials, flags = _arr(partials), _arr(flags, np.uint8)

@@ -20,8 +20,8 @@
  * Field elements are 4 x uint64 little-endian limbs.  "mont" = Montgomery form with R = 2^256, which is the
  * reference's in-memory and key-file representation (Fp_model::mont_repr, MONTGOMERY_OUTPUT); "std" = the plain
  * integer.  G1 affine = x,y (8 limbs); G2 affine = x.a, x.b, y.a, y.b (16 limbs; x = x.a + x.b*u, mcl order).
- * One handle is bound to one CUDA device; calls on one handle must be serialised by the caller (the reference prover
- * is not re-entrant either).  There is no CPU fallback: without a CUDA device b200_init fails with B200_ERR_CUDA.
+ * One handle is bound to one CUDA device (or, from b200_init with n_devices > 1, to one set of devices); calls on one handle
+ * must be serialised by the caller (the reference prover is not re-entrant either).  There is no CPU fallback: without a CUDA device b200_init fails with B200_ERR_CUDA.
  */
 #ifndef B200SNARK_H_
 #define B200SNARK_H_
@@ -55,7 +55,14 @@ typedef struct {
     uint64_t n_rows;
 } b200_csr;
 
-int b200_init(const int* device_ids, int n_devices, b200_ctx** out);   /* n_devices must be 1 (one process per GPU) */
+/* One handle = one device set.  n_devices == 1 (or 0: device 0): a single-GPU context, the form used with one process per
+ * GPU.  n_devices > 1: ONE context owning several GPUs of the box, for callers that are a single process (the reference
+ * prover is a library call, src/stubs.cpp:42-47): keys loaded or assembled on it are split 1/N per device, b200_prove runs on
+ * all of them (one host thread per device issues its launches; the witness and the per-device partial sums travel over peer
+ * memory, so every pair of the devices must have peer access), and returns the same proof as one GPU.  Everything else
+ * (standalone MSM / NTT / field ops, the key generator, r,s proving) runs on the first device. */
+int b200_init(const int* device_ids, int n_devices, b200_ctx** out);
+int b200_device_count(b200_ctx* ctx);
 void b200_shutdown(b200_ctx* ctx);
 const char* b200_strerror(int code);
 const char* b200_last_error(b200_ctx* ctx);
@@ -70,6 +77,8 @@ unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by 
  *   "g2_pair"         G2 accumulate: 2 = one point per lane pair, lazy operand forms (default), 1 = strict forms,
  *                     3 = lazy + out-of-line products, 0 = one thread per point
  *   "finalize_chunks" 1 = stitch chunk partial sums with one thread per chunk edge (default), 0 = one per bucket
+ *   "finalize_big_seg" 1 = buckets spanning many chunks (the "scalar == 1" bucket of 0/1-heavy witnesses) summed in two levels,
+ *                     64 blocks per bucket then one (default); 0 = one block per bucket
  *   "reduce_fold"     stage B of the bucket reduction as halving passes: 1 = for >= 2^17 buckets (default), 2 = always, 0 = never
  *   "pair_reduce"     1 = G2 finalize and bucket-reduction additions with one full addition per lane pair (default), 0 = per thread
  *   "reduce_1d"       1 = running-sum bucket reduction instead of the two-dimensional one
@@ -170,11 +179,32 @@ int b200_prove(b200_key* key, const uint64_t* witness_mont, const uint64_t r_mon
                uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);
 /* coefficients of H, natural order, m entries (h[m-1] = 0), Montgomery */
 int b200_h(b200_key* key, const uint64_t* witness_mont, uint64_t* h_out_mont);
+/* Circuits made of many instances of one master gadget (the reference's r1cs_constraint_light_instance + ITranslator,
+ * LS/relations/constraint_satisfaction_problems/r1cs/r1cs.hpp:145-211, LS/relations/variable.hpp:279-314; used by
+ * src/gadgets/sha256_many.hpp:75-82 and poseidon.hpp:455-462): the constraint system is the plain rows A, B, C (may be empty)
+ * followed, for every instance j in order, by all rows of the master gadget with each variable index v != 0 replaced by
+ * tables[j * table_len + v] (index 0, the constant ONE, is never translated).  The device keeps the master rows once and one
+ * table per instance instead of the flattened rows.  Same proofs as b200_circuit_load on the flattened system. */
+typedef struct {
+    const b200_csr *A, *B, *C;      /* the master gadget's rows; col = master-local variable index < table_len */
+    const uint32_t* tables;         /* n_instances x table_len */
+    uint32_t table_len;
+    uint64_t n_instances;
+} b200_instances;
+int b200_circuit_load_instanced(b200_key* key, const b200_csr* A, const b200_csr* B, const b200_csr* C, const b200_instances* inst,
+                                const uint64_t* coeff_table_mont, size_t n_coeffs, uint32_t num_inputs, uint64_t num_variables);
 /* evaluations of A, B, C on the domain S (m entries each, Montgomery): the witness-times-R1CS step alone */
 int b200_witness_eval(b200_key* key, const uint64_t* witness_mont, uint64_t* a_out, uint64_t* b_out, uint64_t* c_out);
 /* multi-GPU: this rank's partial sums over its key shard — evaluation_At, evaluation_Bt (G2), evaluation_Ht + Lt —
  * as affine Montgomery points: partial[0..7] A, [8..23] B, [24..31] C; flags[3]. */
 int b200_prove_partial(b200_key* key, const uint64_t* witness_mont, uint64_t partial[32], uint8_t flags[3]);
+/* the same, result left ON THE DEVICE: 256 bytes at d_out (A 64 | B 128 | C 64, affine Montgomery, (0,0) = infinity), queued
+ * on b200_stream(ctx) without synchronising, so that a collective on that stream (ncclAllGather) can follow at once; and the
+ * combine of `world` such records that are already on this device.  With these two the exchange of a sharded proof has no
+ * host round trip: partial -> all-gather -> combine -> one 580-byte copy back. */
+int b200_prove_partial_dev(b200_key* key, const uint64_t* witness_mont, void* d_out);
+int b200_proof_combine_dev(b200_key* key, const void* d_parts /*world x 256 B*/, int world,
+                           uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);
 /* sums `world` partials (after an all-gather), adds alpha_g1 / beta_g2, returns the proof points in standard form */
 int b200_proof_combine(b200_key* key, const uint64_t* partials /*world x 32*/, const uint8_t* flags /*world x 3*/, int world,
                        uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);

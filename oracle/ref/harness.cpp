@@ -13,6 +13,8 @@
 #include <chrono>
 #include <omp.h>
 #include <libff/algebra/curves/alt_bn128/alt_bn128_pp.hpp>
+#include <libff/common/rng.hpp>
+#include <libff/algebra/scalar_multiplication/multiexp.hpp>
 #include <libfqfft/evaluation_domain/domains/basic_radix2_domain_aux.hpp>
 #include <libfqfft/evaluation_domain/domains/recursive_domain.hpp>
 #include "r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.hpp"
@@ -40,7 +42,46 @@ int main(int argc, char** argv) {
                   << " L " << full.L_query.size() << "\n";
         return 0;
     }
-    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats [budget_seconds min_repeats]] | --roundtrip-full <pk_in> <pk_out>\n"; return 2; }
+    if (argc >= 5 && std::string(argv[1]) == "--msm") {
+        // CPU column of the standalone MSM sweep (BASELINE.json configs[4]): the reference's own multi_exp (multiexp.tcc:595-627,
+        // uniform scalars - the H-query call) or multi_exp_with_mixed_addition (:631-714, the 0/1 prefilter - the witness calls)
+        // over n distinct bases k_i * G made by the reference's own fixed-base machinery (get_window_table / batch_exp,
+        // multiexp.tcc:771-905).  ref_prove --msm <1|2> <log_n> <repeats> [mix: 0 uniform, 1 = 90 % of the scalars in {0,1}]
+        const int group = atoi(argv[2]), logn = atoi(argv[3]), reps = atoi(argv[4]), mix = argc > 5 ? atoi(argv[5]) : 0;
+        ppT::init_public_params();
+        libff::inhibit_profiling_info = true;
+        libff::inhibit_profiling_counters = true;
+        const size_t n = (size_t)1 << logn, sb = FieldT::size_in_bits();
+        std::vector<FieldT> ks(n), ss(n);
+        for (size_t i = 0; i < n; ++i) {
+            ks[i] = libff::SHA512_rng<FieldT>(((uint64_t)1 << 40) + i);
+            ss[i] = (mix && i % 10) ? ((i / 10 + i) & 1 ? FieldT::one() : FieldT::zero()) : libff::SHA512_rng<FieldT>(i);
+        }
+        libsnark::Config config;
+        std::vector<libff::bigint<FieldT::num_limbs>> scratch;
+        std::vector<double> times;
+        auto run = [&](auto one) {
+            typedef decltype(one) G;
+            const size_t window = libff::get_exp_window_size<G>(n);
+            auto table = libff::get_window_table<G>(sb, window, one);
+            std::vector<G> bases = libff::batch_exp<G, FieldT>(sb, window, table, ks);
+            libff::batch_to_special<G>(bases);
+            for (int r = 0; r < reps; ++r) {
+                auto t0 = std::chrono::steady_clock::now();
+                G res = mix ? libff::multi_exp_with_mixed_addition<G, FieldT, libff::multi_exp_method_BDLO12>(bases.begin(), bases.end(), ss.begin(), ss.end(), scratch, config)
+                            : libff::multi_exp<G, FieldT, libff::multi_exp_method_BDLO12>(bases.begin(), bases.end(), ss.begin(), ss.end(), scratch, config);
+                times.push_back(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+                if (res.is_zero()) std::cerr << "zero result\n";
+            }
+        };
+        if (group == 1) run(libff::G1<ppT>::one()); else run(libff::G2<ppT>::one());
+        std::cout << "{\"group\": \"G" << group << "\", \"log_n\": " << logn << ", \"mix\": " << mix << ", \"threads\": " << omp_get_max_threads()
+                  << ", \"seconds\": [";
+        for (size_t i = 0; i < times.size(); ++i) std::cout << (i ? ", " : "") << times[i];
+        std::cout << "]}\n";
+        return 0;
+    }
+    if (argc < 3) { std::cerr << "usage: ref_prove <problem> <out> [repeats [budget_seconds min_repeats]] | --roundtrip-full <pk_in> <pk_out> | --msm <1|2> <log_n> <repeats> [mix]\n"; return 2; }
     const int repeats = argc > 3 ? atoi(argv[3]) : 1;
     // optional bound for benchmark runs: stop before `repeats` once the prover calls have used budget_seconds, but not
     // before min_repeats of them ran (the number that ran is written to the output)

@@ -20,11 +20,11 @@ for n in (0, 1, 7, 1000, (1 << 20) - 1):
     assert int(allr[0][0]) == 0 and int(allr[-1][1]) == n
     for a, b in zip(allr[:-1], allr[1:]):
         assert int(a[1]) == int(b[0])
-# partial gather: every rank contributes 32 limbs + 3 flags, rank order preserved
-part = np.full(32, rank + 1, dtype=np.uint64); flags = np.array([rank, 0, 1], dtype=np.uint8)
-parts, fl = bench.gather_partials(part, flags, world, device="cpu")
-assert parts.shape == (world, 32) and fl.shape == (world, 3)
-assert all(int(parts[r][0]) == r + 1 and int(fl[r][0]) == r for r in range(world))
+# partial gather: every rank contributes one packed 256-byte record (32 x int64), rank order preserved
+part = torch.full((32,), rank + 1, dtype=torch.int64)
+parts = torch.zeros(32 * world, dtype=torch.int64)
+bench.all_gather_packed(parts, part)
+assert all(int(parts[32 * r]) == r + 1 and int(parts[32 * r + 31]) == r + 1 for r in range(world))
 ms = bench.max_over_ranks(float(rank + 1), device="cpu")
 assert ms == float(world)
 dist.barrier()

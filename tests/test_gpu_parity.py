@@ -500,6 +500,148 @@ def test_sharded_partials_combine_to_same_proof(ctx):
             k.free()
 
 
+def test_sharded_exchange_on_the_device(ctx):
+    """b200_prove_partial_dev / b200_proof_combine_dev: the partial sums stay in HBM (256 B per rank, what an NCCL all-gather
+    moves) and the combine reads the gathered buffer there; world = 2, 3 emulated on one GPU, synthetic and 0/1 witnesses,
+    dense keys (shared digit list over each shard's variable range) and sparse reference-layout keys (one sort per query)."""
+    import torch
+    dev = torch.device("cuda", ctx.device)
+    for make in (lambda: orc.Circuit.synth_field(5000, 2, 7, 8), lambda: orc.Circuit.synth_binary(1000, 10)):
+        circ = make()
+        w = circ.witness()
+        key = orc.Key(circ)
+        want = key.prove(w)
+        mats = [circ.matrix(i) for i in range(3)]
+        for world in (2, 3):
+            gathered = torch.full((32 * world,), -1, dtype=torch.int64, device=dev)
+            keys = [_load(ctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK, rank=r, world=world) for r in range(world)]
+            for r, k in enumerate(keys):
+                k.prove_partial_dev(w, gathered.data_ptr() + 256 * r)
+            got = keys[0].combine_dev(gathered.data_ptr(), world)
+            for g, e in zip(got, want):
+                assert np.array_equal(np.asarray(g), np.asarray(e)), world
+            for k in keys:
+                k.free()
+
+
+def _device_sets():
+    import torch
+    sets = [[0, 0], [0, 0, 0]]                       # the same GPU listed twice / three times: the whole multi-device path on one GPU
+    n = torch.cuda.device_count()
+    if n >= 2:
+        sets.append(list(range(min(n, 8))))
+    return sets
+
+
+def test_multi_device_context_gives_the_one_gpu_proof(ctx):
+    """b200_init with n_devices > 1 (one handle = one device set): a single process, one context, the key split
+    1/N per device, b200_prove on all of them - proofs identical to the oracle's for a key loaded from the reference byte
+    layout and for one assembled from resident base sets, with synthetic and 0/1 witnesses."""
+    for devices in _device_sets():
+        mctx = eb.Context(devices)
+        assert mctx.lib.b200_device_count(mctx.h) == len(devices)
+        try:
+            for make in (lambda: orc.Circuit.synth_field(5000, 2, 7, 8), lambda: orc.Circuit.synth_binary(1000, 10)):
+                circ = make()
+                w = circ.witness()
+                key = orc.Key(circ)
+                want = key.prove(w)
+                pk = _load(mctx, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
+                for _ in range(2):
+                    for g, e in zip(pk.prove(w), want):
+                        assert np.array_equal(np.asarray(g), np.asarray(e)), devices
+                assert np.array_equal(pk.h_poly(w), circ.h_poly(w)[:circ.m])
+                info = pk.info()
+                assert info["nL"] == circ.nv - circ.ni
+                with pytest.raises(eb.B200Error):
+                    pk.prove_partial(w)
+                pk.free()
+        finally:
+            mctx.close()
+
+
+def test_multi_device_context_key_from_bases(ctx):
+    """a key assembled from resident base sets on a multi-device context (what the C++ drop-in does with a reference
+    ProvingKeyT): checked against the closed form in the exponent and against the one-GPU context"""
+    circ = orc.Circuit.synth_field(3000, 1)
+    w = circ.witness()
+    nv, ni, m = circ.nv, circ.ni, circ.m
+    ks = [orc.sha512_rng_fr((1 << 44) + 1000 * i, n) for i, n in enumerate((nv + 1, nv + 1, m - 1, nv - ni))]
+    c1s, c2s = orc.sha512_rng_fr(1 << 45, 3), orc.sha512_rng_fr((1 << 45) + 10, 2)
+    proofs = []
+    for devices in ([0], [0, 0, 0]):
+        c = eb.Context(devices if len(devices) > 1 else devices[0])
+        try:
+            A, B2, H, Lq = eb.Bases(c, 1, scalars=ks[0]), eb.Bases(c, 2, scalars=ks[1]), eb.Bases(c, 1, scalars=ks[2]), eb.Bases(c, 1, scalars=ks[3])
+            c1 = eb.Bases(c, 1, scalars=c1s).download()[0]
+            c2 = eb.Bases(c, 2, scalars=c2s).download()[0]
+            k = eb.ProvingKey.from_bases(c, A, B2, H, Lq, c1, c2, nv, ni)
+            k.load_circuit(circ.matrix(0), circ.matrix(1), circ.matrix(2), circ.coeffs(), ni, nv)
+            proofs.append(k.prove(w))
+            k.free()
+        finally:
+            c.close()
+    for a, b in zip(proofs[0], proofs[1]):
+        assert np.array_equal(np.asarray(a), np.asarray(b))
+
+
+def test_instanced_constraints_on_the_device(ctx):
+    """b200_circuit_load_instanced keeps one master gadget's rows plus a translation table per instance
+    in HBM (r1cs_constraint_light_instance + ITranslator, r1cs.hpp:145-211); witness map, H and the proof equal those of the
+    flattened system (host.append_constraint_instances -> b200_circuit_load) and the oracle's, on 1500 instances, on a
+    single-device and on a multi-device context."""
+    import random
+    H = eb.host
+    rng = random.Random(9)
+    coeffs = [1, 3, 2]
+    # master gadget over local variables 1..4 (0 = ONE): (x1 + 3) * x2 = x3 ; x3 * x3 = x4 + 2 * x1
+    mA = H._csr([[(1, 0), (0, 1)], [(3, 0)]]); mB = H._csr([[(2, 0)], [(3, 0)]]); mC = H._csr([[(3, 0)], [(4, 0), (1, 2)]])
+    master = H.R1CS(0, 4, mA, mB, mC, coeffs)
+    n_inst = 1500
+    nv, ni = 2 + 4 * n_inst, 1
+    plain = (H._csr([[(1, 0)]]), H._csr([[(1, 0)]]), H._csr([[(2, 0)]]))          # x1 * x1 = x2
+    tables = np.array([[0] + [3 + 4 * j + i for i in range(4)] for j in range(n_inst)], dtype=np.uint32)
+    cs = H.R1CS(ni, nv, *plain, coeffs)
+    H.append_constraint_instances(cs, master, [H.Translator(t) for t in tables])
+    vals = [0] * nv
+    x = rng.randrange(H.R_MOD); vals[0] = x; vals[1] = x * x % H.R_MOD
+    for j in range(n_inst):
+        x1, x2 = rng.randrange(H.R_MOD), rng.randrange(2)                        # a 0/1 value in every instance
+        x3 = (x1 + 3) * x2 % H.R_MOD
+        vals[2 + 4 * j: 6 + 4 * j] = [x1, x2, x3, (x3 * x3 - 2 * x1) % H.R_MOD]
+    assert cs.is_satisfied([1] + vals)
+    w = H.fr_to_mont([1] + vals)
+    co = H.fr_to_mont(coeffs)
+    circ = orc.Circuit.from_csr(cs.num_constraints, ni, nv, (cs.A, cs.B, cs.C), co)
+    assert circ.is_satisfied(w)
+    key = orc.Key(circ)
+    want = key.prove(w)
+    h_want, ev = circ.h_poly(w, evals=True)
+    flat_bytes = sum(M[0].nbytes + M[1].nbytes + M[2].nbytes for M in (cs.A, cs.B, cs.C))
+    inst_bytes = tables.nbytes + sum(M[0].nbytes + M[1].nbytes + M[2].nbytes for M in (mA, mB, mC) + plain)
+    print("circuit in HBM / over PCIe: flattened %d B, instanced %d B (%.1fx smaller)" % (flat_bytes, inst_bytes, flat_bytes / inst_bytes))
+    assert inst_bytes * 2 < flat_bytes
+    for c in (ctx, eb.Context([0, 0])):
+        pk = eb.ProvingKey.load(c, key.serialize(orc.FMT_MCL_NOZK), eb.FMT_MCL_NOZK)
+        pk.load_circuit_instanced(*plain, (mA, mB, mC), tables, co, ni, nv)
+        assert pk.info()["m"] == circ.m
+        a, b, cc = pk.witness_eval(w)
+        assert np.array_equal(a, ev[0][:circ.m]) and np.array_equal(b, ev[1][:circ.m]) and np.array_equal(cc, ev[2][:circ.m])
+        assert np.array_equal(pk.h_poly(w), h_want[:circ.m])
+        for g, e in zip(pk.prove(w), want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+        # re-loading the same key with the flattened rows gives the same proof
+        pk.load_circuit(cs.A, cs.B, cs.C, co, ni, nv)
+        for g, e in zip(pk.prove(w), want):
+            assert np.array_equal(np.asarray(g), np.asarray(e))
+        with pytest.raises(eb.B200Error):                                        # a table entry beyond num_variables
+            bad = tables.copy(); bad[7, 2] = nv + 1
+            pk.load_circuit_instanced(*plain, (mA, mB, mC), bad, co, ni, nv)
+        pk.free()
+        if c is not ctx:
+            c.close()
+
+
 def test_host_mirror_prove_json(ctx):
     pb = eb.generate_r1cs_example_with_field_input(200, 2)
     circ = orc.Circuit.synth_field(200, 2)

@@ -61,6 +61,21 @@ def test_shim_fails_loudly_without_a_gpu():
 @needs_shim
 @pytest.mark.parametrize("name", ["sha256", "mimc_merkle", "eddsa"])
 def test_shim_prove_matches_golden_and_passes_the_reference_verifier(name):
+    _prove_and_check(name, {})
+
+
+@pytest.mark.gpu
+@needs_shim
+def test_shim_prove_on_a_multi_device_context():
+    """B200_DEVICES makes the drop-in's one context span several GPUs (b200_init with n_devices > 1): same golden proof.
+    All GPUs of the box when there are several, else the one GPU listed twice (the same code path)."""
+    import torch
+    n = torch.cuda.device_count()
+    devs = ",".join(str(i) for i in range(min(n, 8))) if n >= 2 else "0,0"
+    _prove_and_check("mimc_merkle", {"B200_DEVICES": devs})
+
+
+def _prove_and_check(name, extra_env):
     """BASELINE.json configs[0..2] through the C++ boundary: the JSON string returned by ethsnarks::prove is the committed
     golden proof (the one the reference prover binary reproduces, tests/test_oracle.py) and the reference's own verifier
     accepts it under the oracle key's vk.json, and rejects it under a changed public input."""
@@ -71,7 +86,7 @@ def test_shim_prove_matches_golden_and_passes_the_reference_verifier(name):
         pk, vk, proof = (os.path.join(d, n) for n in ("pk.raw", "vk.json", "proof.json"))
         open(pk, "wb").write(key.serialize(orc.FMT_ALT_NOZK))
         open(vk, "w").write(key.vk_json())
-        res = subprocess.run([SHIM_BIN, "prove", name, pk, proof, vk], capture_output=True, text=True)
+        res = subprocess.run([SHIM_BIN, "prove", name, pk, proof, vk], capture_output=True, text=True, env=dict(os.environ, **extra_env))
         assert res.returncode == 0, res.stdout + res.stderr
         f = _facts(res.stdout)
         assert open(proof).read() == g["proof_json"]
