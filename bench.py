@@ -54,20 +54,45 @@ def all_gather_packed(parts, part, stream=None):
             dist.all_gather_into_tensor(parts, part)
 
 
+class DeviceBuffer:
+    """a device allocation of the library seen as a torch tensor (int64 words) through __cuda_array_interface__"""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 8,), "typestr": "<i8", "data": (int(ptr), False), "version": 2}
+
+
 class ShardedProver:
     """One proof over a key sharded 1/N per rank, with the exchange on the device: every rank queues its partial proof
     (b200_prove_partial_dev: 256 B left in HBM, no synchronisation), the records are all-gathered over NCCL on the library's
     own stream, and rank 0 combines them (b200_proof_combine_dev) and copies the proof back - one host synchronisation per
     proof, on rank 0 only."""
 
-    def __init__(self, key, world, rank, stream, dev):
+    def __init__(self, key, world, rank, stream, dev, staged=True):
         import torch
+        from ethsnarks_b200.lib import chain_owner
         self.key, self.world, self.rank, self.stream = key, world, rank, stream
         self.part = torch.zeros(32, dtype=torch.int64, device=dev)             # 256 B: A 64 | B 128 | C 64
         self.parts = torch.zeros(32 * world, dtype=torch.int64, device=dev)
+        # staged form: the ranks also share the transform work - each of the three evaluation vectors goes through the witness
+        # map and its first two transforms on ONE rank and is broadcast (NCCL, on the library's stream) to the others
+        self.staged = staged and world > 1
+        if self.staged:
+            self.owner = [chain_owner(ch, world) for ch in range(3)]
+            self.chains = sum(1 << ch for ch in range(3) if self.owner[ch] == rank)
+            ptrs, nbytes = key.buffers()
+            self.vecs = [torch.as_tensor(DeviceBuffer(p, nbytes), device=dev) for p in ptrs]
 
     def __call__(self, wptr):
-        self.key.prove_partial_dev(wptr, self.part.data_ptr())
+        if self.staged:
+            import torch
+            import torch.distributed as dist
+            self.key.prove_partial_stage1(wptr, self.chains)
+            with torch.cuda.stream(self.stream):
+                for ch in range(3):
+                    dist.broadcast(self.vecs[ch], src=self.owner[ch])
+            self.key.prove_partial_stage2(self.part.data_ptr())
+        else:
+            self.key.prove_partial_dev(wptr, self.part.data_ptr())
         if self.world > 1:
             all_gather_packed(self.parts, self.part, self.stream)
             src = self.parts
@@ -341,7 +366,7 @@ def run_ours(args):
     w_dev = torch.from_numpy(witness.view(np.int64)).to(dev)            # resident witness (`value`)
     w_pin = torch.from_numpy(witness.view(np.int64)).pin_memory()       # pinned host witness (`e2e`)
 
-    sharded_prove = ShardedProver(key, world, rank, stream, dev) if shard else None
+    sharded_prove = ShardedProver(key, world, rank, stream, dev, staged=bool(args.staged)) if shard else None
 
     def step(wptr):
         return sharded_prove(wptr) if shard else key.prove(wptr)
@@ -494,7 +519,7 @@ def run_ours(args):
         "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "strong" if shard else "weak", "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery)", "data": "synthetic",
         "config": {**workload_config(args.log_m, args.flavour), "num_inputs": dims["ni"], "msm_lengths": {"A": dims["nA"], "B_g2": dims["nB"], "H": dims["nH"], "L": dims["nL"]},
-                   "parallelism": ("ONE proof over a key sharded 1/%d per GPU; 256-byte partial sums all-gathered over NCCL on the device" % world) if shard else
+                   "parallelism": ("ONE proof over a key sharded 1/%d per GPU%s; 256-byte partial sums all-gathered over NCCL on the device" % (world, ", transform chains shared out and broadcast over NCCL" if args.staged else "")) if shard else
                                   (("%d independent replicas" % world if world > 1 else "single GPU") +
                                    (", %d proofs in flight per GPU on one resident key" % len(slots) if len(slots) > 1 else "")),
                    "l2": "inputs larger than L2 (key + sort buffers >> 126 MB per prove)", "r_s": "0,0 (reference no-ZK prover)"},
@@ -534,6 +559,7 @@ def main():
     ap.add_argument("--window", type=int, default=0, help="window size c of the key's fixed-base tables (0 = cost model)")
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (b200_set_option), repeatable")
     ap.add_argument("--in-flight", type=int, default=1, help="prove slots per GPU driven concurrently (1 = one proof at a time)")
+    ap.add_argument("--staged", type=int, default=1, help="sharded proofs: 1 = the ranks also share the transform chains (broadcast of the coset evaluations)")
     ap.add_argument("--verify", type=int, default=1, help="check one proof against its closed form in the exponent (untimed)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -278,6 +278,7 @@ static int init_one(int dev, b200_ctx** out) {
     for (int i = 0; i < 4; ++i) cudaEventCreateWithFlags(&c->lane_done[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_witness, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_shared, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_front, cudaEventDisableTiming);
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
     *out = c;
@@ -299,6 +300,7 @@ static void shutdown_one(b200_ctx* ctx) {
     for (int i = 0; i < 4; ++i) cudaEventDestroy(ctx->lane_done[i]);
     cudaEventDestroy(ctx->ev_witness);
     cudaEventDestroy(ctx->ev_shared);
+    cudaEventDestroy(ctx->ev_front);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -327,6 +329,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "reduce_fold")) ctx->reduce_fold = (int)value;
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
     else if (!strcmp(name, "finalize_big_seg")) ctx->finalize_big_seg = (int)value;
+    else if (!strcmp(name, "split_chains")) ctx->split_chains = (int)value;
     else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;

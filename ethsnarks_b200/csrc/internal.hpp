@@ -56,6 +56,9 @@ struct b200_ctx {
     std::vector<b200_ctx*> peers;
     struct Worker;
     std::vector<Worker*> workers;      // workers[i] drives peers[i]
+    cudaEvent_t ev_front = nullptr;    // "this device's share of the transform chains is done" (multi-device proofs)
+    int split_chains = 1;              // multi-device / multi-rank proofs: the three evaluation vectors' first two transforms are
+                                       // shared out over the devices instead of replicated on each
     cudaEvent_t ev_group = nullptr;    // on a peer: "this device's partial sums have arrived in the first device's gather buffer"
 
     void* scratch(const char* name, size_t bytes);   // throws std::runtime_error on failure
@@ -120,6 +123,8 @@ struct MsmPos {
     void g_scalar_mul_##SUFFIX(b200_ctx* ctx, const void* d_affine_base, const void* d_scalar_mont, void* d_out_xyzz);
 B200_DECL_GROUP(g1)
 B200_DECL_GROUP(g2)
+// one launch: sum of `world` 256-byte partial records + alpha_g1 / beta_g2 -> proof points (standard form) at fin + 0 / 256 / 512
+void g_combine3(b200_ctx* ctx, const void* d_parts, int world, const void* d_alpha_g1, const void* d_beta_g2, void* d_fin);
 // shared list: digits + sort + offsets of n Montgomery scalars for window size c on the current lane (table mode), then one
 // consume per query on any lane that has waited for the prepare
 void msm_shared_prepare(b200_ctx* ctx, const void* d_scalars_mont, size_t n, int c, MsmShared* out);
@@ -168,6 +173,8 @@ void ntt_natural(b200_ctx* ctx, const Domain& dom, void* d_data, int mode);
 // fused H chain: a, b, c hold the evaluations on S (natural order, m entries each); on return c holds the
 // coefficients of H in BIT-REVERSED order (c[p] = h[bitrev(p)]), a and b are clobbered.
 void h_chain(b200_ctx* ctx, const Domain& dom, void* d_a, void* d_b, void* d_c);
+void h_chain_front(b200_ctx* ctx, const Domain& dom, void* const* d_x, int count);      // count of the vectors: S -> coset evaluations
+void h_chain_back(b200_ctx* ctx, const Domain& dom, const void* d_a, const void* d_b, const void* d_c, void* d_out);  // pointwise + icosetFFT
 void bitrev_permute(b200_ctx* ctx, const void* d_in, void* d_out, uint32_t logm, size_t elem_bytes);
 double imad_peak(b200_ctx* ctx, int reps);   // wide 32x32+64 multiply-adds per second, best of reps
 void field_op(b200_ctx* ctx, int field, int op, const void* d_a, const void* d_b, void* d_out, size_t n);

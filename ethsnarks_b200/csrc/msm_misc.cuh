@@ -67,6 +67,33 @@ static void g_sum_strided_t(b200_ctx* ctx, const void* base, size_t stride, int 
     B200_CUDA_CHECK(cudaGetLastError());
 }
 
+// The whole combine of a sharded proof in ONE launch: block 0 adds the world A partials and alpha_g1, block 1 the B partials
+// (G2) and beta_g2, block 2 the C partials; records are 256 bytes apart (A 64 | B 128 | C 64); results in standard form at
+// fin + 0 / + 256 / + 512, each followed by its u32 infinity flag.  (Three launches cost three serial inversions: 0.34 ms.)
+template <typename G>   // instantiated with G2T only, so that one translation unit emits it
+__global__ void g_combine3_kernel(const unsigned char* parts, int world, const Affine<Fq>* alpha, const Affine<Fq2>* beta, unsigned char* fin) {
+    if (threadIdx.x) return;
+    if (blockIdx.x == 1) {
+        XYZZ<Fq2> r = XYZZ<Fq2>::inf();
+        for (int i = 0; i < world; ++i) r.add_mixed(*reinterpret_cast<const Affine<Fq2>*>(parts + (size_t)i * 256 + 64));
+        r.add_mixed(*beta);
+        Affine<Fq2> a = r.to_affine_low_latency();
+        a.x.a = a.x.a.from_mont(); a.x.b = a.x.b.from_mont(); a.y.a = a.y.a.from_mont(); a.y.b = a.y.b.from_mont();
+        *reinterpret_cast<Affine<Fq2>*>(fin + 256) = a;
+        *reinterpret_cast<uint32_t*>(fin + 256 + sizeof(a)) = r.is_inf() ? 1u : 0u;
+        return;
+    }
+    const bool isA = blockIdx.x == 0;
+    XYZZ<Fq> r = XYZZ<Fq>::inf();
+    for (int i = 0; i < world; ++i) r.add_mixed(*reinterpret_cast<const Affine<Fq>*>(parts + (size_t)i * 256 + (isA ? 0 : 192)));
+    if (isA) r.add_mixed(*alpha);
+    Affine<Fq> a = r.to_affine_low_latency();
+    a.x = a.x.from_mont(); a.y = a.y.from_mont();
+    unsigned char* out = fin + (isA ? 0 : 512);
+    *reinterpret_cast<Affine<Fq>*>(out) = a;
+    *reinterpret_cast<uint32_t*>(out + sizeof(a)) = r.is_inf() ? 1u : 0u;
+}
+
 template <typename G>
 static void g_finish_t(b200_ctx* ctx, const void* xt, int nx, const void* at, int na, void* out, bool to_std) {
     g_finish_kernel<G><<<1, 32, 0, ctx->cur()>>>((const typename G::Pt*)xt, nx, (const typename G::Aff*)at, na, (typename G::Aff*)out, to_std);

@@ -343,10 +343,10 @@ __global__ void mul_const_kernel(Fr* data, size_t n, const Fr* __restrict__ c) {
     data[i] = data[i] * (*c);
 }
 // c = (a * b - c) * zinv      (r1cs_to_qap.tcc:282-293)
-__global__ void h_pointwise_kernel(const Fr* __restrict__ a, const Fr* __restrict__ b, Fr* c, size_t n, const Fr* __restrict__ zinv) {
+__global__ void h_pointwise_kernel(const Fr* __restrict__ a, const Fr* __restrict__ b, const Fr* c, Fr* out, size_t n, const Fr* __restrict__ zinv) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    c[i] = (a[i] * b[i] - c[i]) * (*zinv);
+    out[i] = (a[i] * b[i] - c[i]) * (*zinv);      // out may be c itself
 }
 
 void ntt_natural(b200_ctx* ctx, const Domain& dom, void* d_data, int mode) {
@@ -374,10 +374,28 @@ void h_chain(b200_ctx* ctx, const Domain& dom, void* d_a, void* d_b, void* d_c) 
     run_transform<true>(ctx, logm, a, b, c, 3, (const Fr*)dom.tw_inv, (const Fr*)dom.cs_fwd);
     // evaluations on the coset g<omega> (natural order)
     run_transform<false>(ctx, logm, a, b, c, 3, (const Fr*)dom.tw_fwd, nullptr);
-    h_pointwise_kernel<<<(unsigned)((m + 127) / 128), 128, 0, ctx->stream>>>(a, b, c, m, (const Fr*)dom.zinv + 3);
+    h_pointwise_kernel<<<(unsigned)((m + 127) / 128), 128, 0, ctx->stream>>>(a, b, c, c, m, (const Fr*)dom.zinv + 3);
     ctx->launches++;
     // icosetFFT, output left in bit-reversed order
     run_transform<true>(ctx, logm, c, nullptr, nullptr, 1, (const Fr*)dom.tw_inv, (const Fr*)dom.cs_inv);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+
+// The same chain in two halves, for a proof spread over several GPUs: h_chain_front takes ONE of the three evaluation vectors
+// (or two) to its evaluations on the coset (iFFT then cosetFFT) - the three vectors are independent up to here, so different GPUs can
+// take one each; h_chain_back is the pointwise step and the final icosetFFT once all three are present.
+void h_chain_front(b200_ctx* ctx, const Domain& dom, void* const* d_x, int count) {
+    if (count < 1) return;
+    Fr* x[3] = {(Fr*)d_x[0], count > 1 ? (Fr*)d_x[1] : nullptr, count > 2 ? (Fr*)d_x[2] : nullptr};
+    run_transform<true>(ctx, dom.logm, x[0], x[1], x[2], count, (const Fr*)dom.tw_inv, (const Fr*)dom.cs_fwd);
+    run_transform<false>(ctx, dom.logm, x[0], x[1], x[2], count, (const Fr*)dom.tw_fwd, nullptr);
+    B200_CUDA_CHECK(cudaGetLastError());
+}
+void h_chain_back(b200_ctx* ctx, const Domain& dom, const void* d_a, const void* d_b, const void* d_c, void* d_out) {
+    const size_t m = (size_t)1 << dom.logm;
+    h_pointwise_kernel<<<(unsigned)((m + 127) / 128), 128, 0, ctx->stream>>>((const Fr*)d_a, (const Fr*)d_b, (const Fr*)d_c, (Fr*)d_out, m, (const Fr*)dom.zinv + 3);
+    ctx->launches++;
+    run_transform<true>(ctx, dom.logm, (Fr*)d_out, nullptr, nullptr, 1, (const Fr*)dom.tw_inv, (const Fr*)dom.cs_inv);
     B200_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -56,6 +56,8 @@ struct b200_key {
     void* coeffs = nullptr;
     Domain dom;
     void *d_w = nullptr, *d_a = nullptr, *d_b = nullptr, *d_c = nullptr;
+    void* d_h = nullptr;        // staged (multi-GPU) proofs: H's coefficients, so that d_c - which other devices may still be
+                                // reading - is not overwritten
     uint64_t H_total = 0;       // |H_query| in the key file
     // a key on a multi-device context: one shard per device (shards[i] on ctx->peers[i - 1], shards[0] on ctx); the
     // wrapper itself holds no device memory
@@ -151,7 +153,7 @@ void key_release(b200_key* k) {
         return;
     }
     if (k->attached) {
-        cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
+        cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c); cudaFree(k->d_h);
         delete k;
         return;
     }
@@ -163,7 +165,7 @@ void key_release(b200_key* k) {
     cudaFree(k->inst_tables);
     cudaFree(k->coeffs);
     if (k->has_circuit) domain_free(&k->dom);
-    cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
+    cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c); cudaFree(k->d_h);
     delete k;
 }
 
@@ -578,7 +580,7 @@ int b200_key_attach(b200_key* key, b200_ctx* ctx, b200_key** out) {
         k->attached = true;
         k->ctx = ctx;
         k->H_host.clear();
-        k->d_w = k->d_a = k->d_b = k->d_c = nullptr;
+        k->d_w = k->d_a = k->d_b = k->d_c = k->d_h = nullptr;
         B200_CUDA_CHECK(cudaMalloc(&k->d_w, (k->nv + 1) * 32));
         B200_CUDA_CHECK(cudaMalloc(&k->d_a, k->m * 32));
         B200_CUDA_CHECK(cudaMalloc(&k->d_b, k->m * 32));
@@ -663,8 +665,8 @@ static int circuit_load_impl(b200_key* k, const b200_csr* A, const b200_csr* B, 
             cudaFree(k->inst_tables); k->inst_tables = nullptr; k->n_inst = 0; k->inst_tlen = 0;
             cudaFree(k->coeffs); k->coeffs = nullptr;
             domain_free(&k->dom);
-            cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c);
-            k->d_w = k->d_a = k->d_b = k->d_c = nullptr;
+            cudaFree(k->d_w); cudaFree(k->d_a); cudaFree(k->d_b); cudaFree(k->d_c); cudaFree(k->d_h);
+            k->d_w = k->d_a = k->d_b = k->d_c = k->d_h = nullptr;
             k->has_circuit = false;
         }
         k->n_plain = A->n_rows;
@@ -817,7 +819,7 @@ int b200_generate_key(b200_ctx* ctx, const b200_csr* A, const b200_csr* B, const
 // ------------------------------------------------------------------------------------------------ prove
 namespace {
 
-void run_witness_eval(b200_key* k, const uint64_t* witness) {
+void run_witness_eval(b200_key* k, const uint64_t* witness, int chains = 7) {
     b200_ctx* ctx = k->ctx;
     ctx->t_begin("h2d.witness");
     if (witness) B200_CUDA_CHECK(cudaMemcpyAsync(k->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
@@ -826,6 +828,7 @@ void run_witness_eval(b200_key* k, const uint64_t* witness) {
     ctx->t_begin("witness_eval");
     void* outs[3] = {k->d_a, k->d_b, k->d_c};
     for (int i = 0; i < 3; ++i) {
+        if (!((chains >> i) & 1)) continue;
         spmv(ctx, k->M[i], k->coeffs, k->d_w, outs[i]);
         if (k->n_inst) spmv_instances(ctx, k->Mi[i], k->coeffs, k->d_w, k->inst_tables, k->inst_tlen, k->n_inst, (char*)outs[i] + k->n_plain * 32);
     }
@@ -923,10 +926,11 @@ void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1, int finish =
         lane_end();
     } catch (...) { ctx->lane = 0; throw; }
 }
-void run_msm_h_and_join(b200_key* k, const Acc& a) {
+void run_msm_h_and_join(b200_key* k, const Acc& a, const void* d_hcoef = nullptr) {
     b200_ctx* ctx = k->ctx;
+    if (!d_hcoef) d_hcoef = k->d_c;
     ctx->t_begin("msm.H");
-    msm_run(ctx, 1, k->H_t ? k->H_t : k->H, (const char*)k->d_c + k->H_lo * 32, nullptr, k->nH, true, a.H, k->H_t ? k->cH : 0, k->nH);
+    msm_run(ctx, 1, k->H_t ? k->H_t : k->H, (const char*)d_hcoef + k->H_lo * 32, nullptr, k->nH, true, a.H, k->H_t ? k->cH : 0, k->nH);
     ctx->t_end();
     if (ctx->overlap)
         for (int lane = 1; lane < 4; ++lane) B200_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->lane_done[lane], 0));
@@ -957,6 +961,46 @@ char* partial_async(b200_key* k, const uint64_t* witness) {
     ctx->t_end();
     return fin;
 }
+// The same in two stages, for a proof spread over several GPUs (or ranks) that share the transform work: stage 1 uploads the
+// witness, queues the witness-only MSMs on their lanes, and takes only the evaluation vectors named in `chains` (bit 0 = A,
+// 1 = B, 2 = C) through the witness map and the first two transforms; the caller then makes all three vectors of coset
+// evaluations present on every device (broadcast from their owners: k->d_a / d_b / d_c); stage 2 is the pointwise step, the
+// final transform, the H MSM and the finishes.
+void partial_stage1(b200_key* k, const uint64_t* witness, int chains) {
+    b200_ctx* ctx = k->ctx;
+    ctx->t_begin("prove.total");
+    Acc a = acc_slots(ctx);
+    run_witness_eval(k, witness, chains);
+    run_msms_witness_only(k, a, false, 2);
+    void* bufs[3];
+    int n = 0;
+    if (chains & 1) bufs[n++] = k->d_a;
+    if (chains & 2) bufs[n++] = k->d_b;
+    if (chains & 4) bufs[n++] = k->d_c;
+    ctx->t_begin("h_chain.front");
+    h_chain_front(ctx, k->dom, bufs, n);
+    ctx->t_end();
+}
+char* partial_stage2(b200_key* k) {
+    b200_ctx* ctx = k->ctx;
+    Acc a = acc_slots(ctx);
+    if (!k->d_h) B200_CUDA_CHECK(cudaMalloc(&k->d_h, k->m * 32));
+    ctx->t_begin("h_chain.back");
+    h_chain_back(ctx, k->dom, k->d_a, k->d_b, k->d_c, k->d_h);
+    ctx->t_end();
+    run_msm_h_and_join(k, a, k->d_h);
+    char* fin = (char*)a.fin;
+    g_finish(ctx, 1, a.H, 2, nullptr, 0, fin + 512, false);
+    ctx->t_end();
+    return fin;
+}
+// which rank / device takes evaluation vector ch (0 = A, 1 = B, 2 = C) through the first two transforms
+inline int chain_owner(int ch, int world) { return world >= 3 ? ch : (world == 2 ? (ch == 1 ? 1 : 0) : 0); }
+inline int chains_of(int rank, int world) {
+    int m = 0;
+    for (int ch = 0; ch < 3; ++ch) if (chain_owner(ch, world) == rank) m |= 1 << ch;
+    return m;
+}
 // A 64 B | B 128 B | C 64 B (the point at infinity is (0,0)) to dst, which may be on another device (peer memory)
 void pack_partial(b200_ctx* ctx, const char* fin, void* dst) {
     B200_CUDA_CHECK(cudaMemcpyAsync(dst, fin, 64, cudaMemcpyDefault, ctx->stream));
@@ -967,9 +1011,7 @@ void pack_partial(b200_ctx* ctx, const char* fin, void* dst) {
 char* combine_async(b200_key* k, const void* d_parts, int world) {
     b200_ctx* ctx = k->ctx;
     char* fin = (char*)acc_slots(ctx).fin + 2048;
-    g_sum_strided(ctx, 1, d_parts, 256, world, k->consts_g1, fin, true);
-    g_sum_strided(ctx, 2, (const char*)d_parts + 64, 256, world, k->consts_g2, fin + 256, true);
-    g_sum_strided(ctx, 1, (const char*)d_parts + 192, 256, world, nullptr, fin + 512, true);
+    g_combine3(ctx, d_parts, world, k->consts_g1, k->consts_g2, fin);
     return fin;
 }
 
@@ -1025,11 +1067,32 @@ int b200_prove(b200_key* k, const uint64_t* witness, const uint64_t r[4], const 
             B200_CUDA_CHECK(cudaMemcpyAsync(k0->d_w, witness, (k->nv + 1) * 32, cudaMemcpyDefault, ctx->stream));
             cudaEvent_t ev_w = ctx->ev_group;
             B200_CUDA_CHECK(cudaEventRecord(ev_w, ctx->stream));
+            const int world = k->world;
+            const size_t vec_bytes = (size_t)k->m * 32;
+            // stage 1 everywhere: MSM lanes + this device's share of the three transform chains; "front done" events
             for_each_device(ctx, [&](int i) {
                 b200_key* ki = k->shards[i];
                 b200_ctx* ci = ki->ctx;
                 if (i) B200_CUDA_CHECK(cudaStreamWaitEvent(ci->stream, ev_w, 0));
-                char* fin = partial_async(ki, i ? (const uint64_t*)k0->d_w : nullptr);
+                partial_stage1(ki, i ? (const uint64_t*)k0->d_w : nullptr, ctx->split_chains ? chains_of(i, world) : 7);
+                B200_CUDA_CHECK(cudaEventRecord(ci->ev_front, ci->stream));
+            });
+            // every device pulls the coset evaluations it did not compute from their owners over peer memory, then stage 2
+            for_each_device(ctx, [&](int i) {
+                b200_key* ki = k->shards[i];
+                b200_ctx* ci = ki->ctx;
+                if (ctx->split_chains) {
+                    void* mine[3] = {ki->d_a, ki->d_b, ki->d_c};
+                    for (int ch = 0; ch < 3; ++ch) {
+                        const int o = chain_owner(ch, world);
+                        if (o == i) continue;
+                        b200_key* ko = k->shards[o];
+                        void* theirs[3] = {ko->d_a, ko->d_b, ko->d_c};
+                        B200_CUDA_CHECK(cudaStreamWaitEvent(ci->stream, ko->ctx->ev_front, 0));
+                        B200_CUDA_CHECK(cudaMemcpyPeerAsync(mine[ch], ci->device, theirs[ch], ko->ctx->device, vec_bytes, ci->stream));
+                    }
+                }
+                char* fin = partial_stage2(ki);
                 pack_partial(ci, fin, (char*)k->gather + (size_t)i * 256);
                 if (i) B200_CUDA_CHECK(cudaEventRecord(ci->ev_group, ci->stream));
             });
@@ -1118,6 +1181,33 @@ int b200_prove_partial_dev(b200_key* k, const uint64_t* witness, void* d_out) {
     if (!k->shards.empty()) { ctx->last_error = "prove_partial on a multi-device context: b200_prove runs all devices"; return B200_ERR_STATE; }
     return Guard{ctx}.run([&] {
         char* fin = partial_async(k, witness);
+        pack_partial(ctx, fin, d_out);
+        return (int)B200_OK;
+    });
+}
+// The staged form for ranks that share the transform work (see partial_stage1): stage 1 with this rank's share of the three
+// evaluation vectors (chains: bit 0 = A, 1 = B, 2 = C; b200_chain_owner says which rank takes which), then the caller
+// broadcasts each vector of coset evaluations from its owner to all ranks (the device buffers come from b200_key_buffers;
+// ncclBroadcast on b200_stream(ctx)), then stage 2, which leaves the same 256-byte record as b200_prove_partial_dev.
+int b200_chain_owner(int chain, int world) { return (chain < 0 || chain > 2 || world < 1) ? -1 : chain_owner(chain, world); }
+int b200_key_buffers(b200_key* k, void* bufs[3], size_t* bytes_each) {
+    if (!k || !bufs || !bytes_each || !k->has_circuit || !k->shards.empty()) return B200_ERR_ARG;
+    bufs[0] = k->d_a; bufs[1] = k->d_b; bufs[2] = k->d_c;
+    *bytes_each = (size_t)k->m * 32;
+    return B200_OK;
+}
+int b200_prove_partial_stage1(b200_key* k, const uint64_t* witness, int chains) {
+    if (!k || !witness || chains < 0 || chains > 7) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (!k->has_circuit || !k->shards.empty()) { ctx->last_error = "prove_partial_stage1: needs a single-device key with a circuit"; return B200_ERR_STATE; }
+    return Guard{ctx}.run([&] { partial_stage1(k, witness, chains); return (int)B200_OK; });
+}
+int b200_prove_partial_stage2(b200_key* k, void* d_out) {
+    if (!k || !d_out) return B200_ERR_ARG;
+    b200_ctx* ctx = k->ctx;
+    if (!k->has_circuit || !k->shards.empty()) return B200_ERR_STATE;
+    return Guard{ctx}.run([&] {
+        char* fin = partial_stage2(k);
         pack_partial(ctx, fin, d_out);
         return (int)B200_OK;
     });

@@ -28,7 +28,7 @@ SYMBOLS = [
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
     "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
-    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc", "b200_device_count", "b200_circuit_load_instanced", "b200_prove_partial_dev", "b200_proof_combine_dev",
+    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc", "b200_device_count", "b200_chain_owner", "b200_key_buffers", "b200_prove_partial_stage1", "b200_prove_partial_stage2", "b200_circuit_load_instanced", "b200_prove_partial_dev", "b200_proof_combine_dev",
 ]
 
 
@@ -46,6 +46,11 @@ class B200Error(RuntimeError):
 
 
 _lib = None
+
+
+def chain_owner(chain, world):
+    """rank that takes evaluation vector `chain` (0 = A, 1 = B, 2 = C) through its first two transforms in a staged proof"""
+    return int(load().b200_chain_owner(chain, world))
 
 
 def load():
@@ -430,6 +435,20 @@ class ProvingKey:
         context's stream without synchronising"""
         wp, keep = self._wptr(witness)
         self.ctx.check(self.ctx.lib.b200_prove_partial_dev(self.h, wp, C.c_void_p(d_out_ptr)), "prove_partial_dev")
+
+    def buffers(self):
+        """device pointers of the three evaluation vectors (A, B, C) and their size in bytes"""
+        bufs = (C.c_void_p * 3)()
+        n = C.c_size_t()
+        self.ctx.check(self.ctx.lib.b200_key_buffers(self.h, bufs, C.byref(n)), "key_buffers")
+        return [int(b) for b in bufs], int(n.value)
+
+    def prove_partial_stage1(self, witness, chains):
+        wp, keep = self._wptr(witness)
+        self.ctx.check(self.ctx.lib.b200_prove_partial_stage1(self.h, wp, C.c_int(chains)), "prove_partial_stage1")
+
+    def prove_partial_stage2(self, d_out_ptr):
+        self.ctx.check(self.ctx.lib.b200_prove_partial_stage2(self.h, C.c_void_p(d_out_ptr)), "prove_partial_stage2")
 
     def combine_dev(self, d_parts_ptr, world):
         """b200_proof_combine_dev: `world` packed partials already on this device -> the proof (standard form)"""

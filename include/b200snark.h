@@ -77,6 +77,8 @@ unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by 
  *   "g2_pair"         G2 accumulate: 2 = one point per lane pair, lazy operand forms (default), 1 = strict forms,
  *                     3 = lazy + out-of-line products, 0 = one thread per point
  *   "finalize_chunks" 1 = stitch chunk partial sums with one thread per chunk edge (default), 0 = one per bucket
+ *   "split_chains"    1 = a multi-device context shares the first two transforms of the three evaluation vectors out over its
+ *                     devices (default); 0 = every device runs all of them
  *   "finalize_big_seg" 1 = buckets spanning many chunks (the "scalar == 1" bucket of 0/1-heavy witnesses) summed in two levels,
  *                     64 blocks per bucket then one (default); 0 = one block per bucket
  *   "reduce_fold"     stage B of the bucket reduction as halving passes: 1 = for >= 2^17 buckets (default), 2 = always, 0 = never
@@ -205,6 +207,15 @@ int b200_prove_partial(b200_key* key, const uint64_t* witness_mont, uint64_t par
 int b200_prove_partial_dev(b200_key* key, const uint64_t* witness_mont, void* d_out);
 int b200_proof_combine_dev(b200_key* key, const void* d_parts /*world x 256 B*/, int world,
                            uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);
+/* The staged form, for ranks that also share the TRANSFORM work of one proof: the three evaluation vectors A, B, C go through the
+ * witness map and their first two transforms on different ranks (b200_chain_owner(chain, world): 0 = A, 1 = B, 2 = C), the
+ * caller broadcasts each vector of coset evaluations from its owner to all ranks (device buffers of m x 32 bytes from
+ * b200_key_buffers; ncclBroadcast on b200_stream(ctx)), and stage 2 - pointwise step, last transform, H MSM - leaves the same
+ * 256-byte record as b200_prove_partial_dev.  Nothing synchronises.  chains: bit 0 = A, 1 = B, 2 = C (7 = all, no sharing). */
+int b200_chain_owner(int chain, int world);
+int b200_key_buffers(b200_key* key, void* bufs[3], size_t* bytes_each);
+int b200_prove_partial_stage1(b200_key* key, const uint64_t* witness_mont, int chains);
+int b200_prove_partial_stage2(b200_key* key, void* d_out);
 /* sums `world` partials (after an all-gather), adds alpha_g1 / beta_g2, returns the proof points in standard form */
 int b200_proof_combine(b200_key* key, const uint64_t* partials /*world x 32*/, const uint8_t* flags /*world x 3*/, int world,
                        uint64_t A_xy[8], uint64_t B_xy[16], uint64_t C_xy[8], uint8_t infinity_flags[3]);

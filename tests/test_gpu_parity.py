@@ -524,6 +524,48 @@ def test_sharded_exchange_on_the_device(ctx):
                 k.free()
 
 
+def test_staged_sharded_proof_shares_the_transform_chains(ctx):
+    """b200_prove_partial_stage1 / stage2: the ranks of a sharded proof also share the transform work - each evaluation vector
+    goes through the witness map and its first two transforms on its owner only and is then copied to the others (what
+    ncclBroadcast does between real ranks; here world = 2, 3, 4 on one GPU with device-to-device copies)."""
+    import torch
+    import bench
+    dev = torch.device("cuda", ctx.device)
+    circ = orc.Circuit.synth_field(5000, 2, 7, 8)
+    w = circ.witness()
+    key = orc.Key(circ)
+    want = key.prove(w)
+    for world in (2, 3, 4):
+        owners = [L.chain_owner(ch, world) for ch in range(3)]
+        assert sorted(set(owners)) == list(range(min(world, 3)))
+        ctxs = [eb.Context(ctx.device) for _ in range(world)]        # one context per emulated rank (the result slots are per context)
+        keys = [_load(ctxs[r], circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK, rank=r, world=world) for r in range(world)]
+        vecs = []
+        for k in keys:
+            ptrs, nbytes = k.buffers()
+            assert nbytes == circ.m * 32
+            vecs.append([torch.as_tensor(bench.DeviceBuffer(p, nbytes), device=dev) for p in ptrs])
+        gathered = torch.full((32 * world,), -1, dtype=torch.int64, device=dev)
+        for r, k in enumerate(keys):
+            k.prove_partial_stage1(w, sum(1 << ch for ch in range(3) if owners[ch] == r))
+        torch.cuda.synchronize()
+        for ch in range(3):                                   # the broadcast
+            for r in range(world):
+                if r != owners[ch]:
+                    vecs[r][ch].copy_(vecs[owners[ch]][ch])
+        torch.cuda.synchronize()
+        for r, k in enumerate(keys):
+            k.prove_partial_stage2(gathered.data_ptr() + 256 * r)
+        torch.cuda.synchronize()
+        got = keys[0].combine_dev(gathered.data_ptr(), world)
+        for g, e in zip(got, want):
+            assert np.array_equal(np.asarray(g), np.asarray(e)), world
+        for k in keys:
+            k.free()
+        for c in ctxs:
+            c.close()
+
+
 def _device_sets():
     import torch
     sets = [[0, 0], [0, 0, 0]]                       # the same GPU listed twice / three times: the whole multi-device path on one GPU
