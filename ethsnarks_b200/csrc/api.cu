@@ -327,6 +327,7 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "shared_sort")) ctx->shared_sort = (int)value;
     else if (!strcmp(name, "pair_reduce")) ctx->pair_reduce = (int)value;
     else if (!strcmp(name, "reduce_fold")) ctx->reduce_fold = (int)value;
+    else if (!strcmp(name, "pair_tail")) ctx->pair_tail = (int)value;
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
     else if (!strcmp(name, "finalize_big_seg")) ctx->finalize_big_seg = (int)value;
     else if (!strcmp(name, "split_chains")) ctx->split_chains = (int)value;

@@ -38,6 +38,7 @@ struct b200_ctx {
                                        // queries are dense and their tables share a window size
     cudaEvent_t ev_shared = nullptr;
     int pair_reduce = 1;               // 1 = G2 finalize and stages A, B of the bucket reduction with one full addition per lane pair
+    int pair_tail = 1;                 // 1 = the latency-bound stages B - E of the G2 bucket reduction with one point per lane pair too
     int reduce_fold = 1;               // stage B of the 2D bucket reduction as halving passes (msm_rc_fold): 1 = for bucket sets of
                                        // >= 2^17 (measured: pays from there on, costs ~20 us of extra launches below), 2 = always, 0 = never
     int reduce_1d = 0;                 // 1 = running-sum bucket reduction instead of the two-dimensional one

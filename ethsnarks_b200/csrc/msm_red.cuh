@@ -396,6 +396,84 @@ __global__ void __launch_bounds__(32) msm_rc_final(const typename G::Pt* __restr
     if (threadIdx.x == 0) out[blockIdx.x] = acc;
 }
 
+// ---- stages B - E for G2 with one point per LANE PAIR (16 points per warp).  These stages are chains of dependent group
+// operations in a few warps; a lone warp is bound by its own IMAD issue rate, so halving the instructions per operation
+// (each lane of a pair computes one Fq2 component, msm_acc_pair.cuh) halves the latency of every link of the chain.
+template <int MODE>
+B200_DEV void warp_tree_reduce_pair(const PairLane<MODE>& ln, HalfXYZZ& acc) {      // result in pair 0 (lanes 0, 1)
+    const uint32_t pair = (threadIdx.x & 31) >> 1;
+#pragma unroll 1
+    for (int off = 8; off > 0; off >>= 1) {
+        HalfXYZZ other;
+        uint32_t* o = reinterpret_cast<uint32_t*>(&other);
+        const uint32_t* a = reinterpret_cast<const uint32_t*>(&acc);
+#pragma unroll
+        for (int w = 0; w < (int)(sizeof(HalfXYZZ) / 4); ++w) o[w] = __shfl_down_sync(0xffffffffu, a[w], 2 * off);
+        if (pair < (uint32_t)off) pair_add_full(ln, acc, other);
+    }
+}
+B200_DEV PairLane<2> warp_pair_lane() {
+    PairLane<2> ln;
+    ln.imag = threadIdx.x & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    return ln;
+}
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_sum_pair(const G2XYZZ* __restrict__ pc, const G2XYZZ* __restrict__ pr, uint32_t half, uint32_t s, uint32_t K,
+                                                      G2XYZZ* __restrict__ V) {
+    const uint32_t S = 1u << s, Rn = half >> s;
+    const uint32_t Kc = min(K, Rn), Kr = min(K, S);
+    const uint32_t ncol = (Rn / Kc) * S, nrow = Rn * (S / Kr);
+    const uint32_t o = blockIdx.x;
+    const G2XYZZ* src;
+    uint32_t cnt, stride;
+    if (o < S) { src = pc + (size_t)blockIdx.y * ncol + o; cnt = Rn / Kc; stride = S; }
+    else { src = pr + (size_t)blockIdx.y * nrow + (size_t)(o - S) * (S / Kr); cnt = S / Kr; stride = 1; }
+    const PairLane<2> ln = warp_pair_lane();
+    HalfXYZZ acc = ln.inf();
+    for (uint32_t t = threadIdx.x >> 1; t < cnt; t += 16) pair_add_full(ln, acc, pair_load(src + (size_t)t * stride, ln.imag));
+    warp_tree_reduce_pair(ln, acc);
+    if (threadIdx.x < 2) pair_store(&V[(size_t)blockIdx.y * (S + Rn) + o], ln.imag, acc);
+}
+#define B200_RC_SLICE_PAIR 64
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_bits_pair(const G2XYZZ* __restrict__ V, uint32_t half, uint32_t s, uint32_t nbits, uint32_t nslice,
+                                                       G2XYZZ* __restrict__ Us) {
+    const uint32_t S = 1u << s, Rn = half >> s;
+    const uint32_t i = blockIdx.x / nslice, sl = blockIdx.x % nslice;
+    const G2XYZZ* v = V + (size_t)blockIdx.z * (S + Rn);
+    const PairLane<2> ln = warp_pair_lane();
+    HalfXYZZ acc = ln.inf();
+    const uint32_t end = min((sl + 1) * B200_RC_SLICE_PAIR, S + Rn);
+    for (uint32_t t = sl * B200_RC_SLICE_PAIR + (threadIdx.x >> 1); t < end; t += 16) {
+        const uint32_t weight = t < S ? t + 1 : (t - S) << s;
+        if ((weight >> i) & 1u) pair_add_full(ln, acc, pair_load(&v[t], ln.imag));
+    }
+    warp_tree_reduce_pair(ln, acc);
+    if (threadIdx.x < 2) pair_store(&Us[((size_t)blockIdx.z * nbits + i) * nslice + sl], ln.imag, acc);
+}
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_shift_pair(const G2XYZZ* __restrict__ Us, uint32_t nbits, uint32_t nslice, G2XYZZ* __restrict__ U) {
+    const uint32_t i = blockIdx.x;
+    const G2XYZZ* src = Us + ((size_t)blockIdx.z * nbits + i) * nslice;
+    const PairLane<2> ln = warp_pair_lane();
+    HalfXYZZ acc = ln.inf();
+    for (uint32_t t = threadIdx.x >> 1; t < nslice; t += 16) pair_add_full(ln, acc, pair_load(&src[t], ln.imag));
+    warp_tree_reduce_pair(ln, acc);
+    if (threadIdx.x < 2) {
+        for (uint32_t k = 0; k < i; ++k) acc = pair_dbl(ln, acc);
+        pair_store(&U[(size_t)blockIdx.z * nbits + i], ln.imag, acc);
+    }
+}
+template <typename G>
+__global__ void __launch_bounds__(32) msm_rc_final_pair(const G2XYZZ* __restrict__ U, uint32_t nbits, G2XYZZ* __restrict__ out) {
+    const PairLane<2> ln = warp_pair_lane();
+    HalfXYZZ acc = ln.inf();
+    for (uint32_t t = threadIdx.x >> 1; t < nbits; t += 16) pair_add_full(ln, acc, pair_load(&U[(size_t)blockIdx.x * nbits + t], ln.imag));
+    warp_tree_reduce_pair(ln, acc);
+    if (threadIdx.x < 2) pair_store(&out[blockIdx.x], ln.imag, acc);
+}
+
 // final = sum_k 2^(c k) win[k]   (the reference's combine, multiexp.tcc:583-592)
 template <typename G>
 __global__ void msm_horner(const typename G::Pt* __restrict__ win, int W, int c, typename G::Pt* __restrict__ out) {
@@ -461,10 +539,11 @@ void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void*
         Pt* pr = (Pt*)ctx->scratch("msm_rc_pr", (size_t)Wr * nrow * sizeof(Pt));
         Pt* V = (Pt*)ctx->scratch("msm_rc_v", (size_t)Wr * (S + Rn) * sizeof(Pt));
         Pt* U = (Pt*)ctx->scratch("msm_rc_u", (size_t)Wr * nbits * sizeof(Pt));
-        const uint32_t nslice = (S + Rn + B200_RC_SLICE - 1) / B200_RC_SLICE;
+        bool pair_a = false, pair_t = false;
+        if constexpr (sizeof(Pt) > 128) { pair_a = ctx->pair_reduce != 0; pair_t = ctx->pair_reduce != 0 && ctx->pair_tail != 0; }
+        const uint32_t slice = pair_t ? B200_RC_SLICE_PAIR : B200_RC_SLICE;
+        const uint32_t nslice = (S + Rn + slice - 1) / slice;
         Pt* Us = (Pt*)ctx->scratch("msm_rc_us", (size_t)Wr * nbits * nslice * sizeof(Pt));
-        bool pair_a = false;
-        if constexpr (sizeof(Pt) > 128) pair_a = ctx->pair_reduce != 0;
         if constexpr (sizeof(Pt) > 128) {
             if (pair_a) msm_rc_partial_pair<G><<<dim3((2 * (ncol + nrow) + 127) / 128, Wr), 128, 0, st>>>((const G2XYZZ*)B, p.half, s, K, (G2XYZZ*)pc, (G2XYZZ*)pr);
         }
@@ -489,11 +568,23 @@ void launch_reduce(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const void*
             }
             ctx->launches--;      // the common count below assumes one stage-B launch
         } else {
-            msm_rc_sum<G><<<dim3(S + Rn, Wr), 32, 0, st>>>(pc, pr, p.half, s, K, V);
+            if constexpr (sizeof(Pt) > 128) {
+                if (pair_t) msm_rc_sum_pair<G><<<dim3(S + Rn, Wr), 32, 0, st>>>((const G2XYZZ*)pc, (const G2XYZZ*)pr, p.half, s, K, (G2XYZZ*)V);
+            }
+            if (!pair_t) msm_rc_sum<G><<<dim3(S + Rn, Wr), 32, 0, st>>>(pc, pr, p.half, s, K, V);
         }
-        msm_rc_bits<G><<<dim3(nbits * nslice, 1, Wr), 32, 0, st>>>(V, p.half, s, nbits, nslice, Us);
-        msm_rc_shift<G><<<dim3(nbits, 1, Wr), 32, 0, st>>>(Us, nbits, nslice, U);
-        msm_rc_final<G><<<Wr, 32, 0, st>>>(U, nbits, p.table ? (Pt*)d_out : win);
+        if constexpr (sizeof(Pt) > 128) {
+            if (pair_t) {
+                msm_rc_bits_pair<G><<<dim3(nbits * nslice, 1, Wr), 32, 0, st>>>((const G2XYZZ*)V, p.half, s, nbits, nslice, (G2XYZZ*)Us);
+                msm_rc_shift_pair<G><<<dim3(nbits, 1, Wr), 32, 0, st>>>((const G2XYZZ*)Us, nbits, nslice, (G2XYZZ*)U);
+                msm_rc_final_pair<G><<<Wr, 32, 0, st>>>((const G2XYZZ*)U, nbits, (G2XYZZ*)(p.table ? (Pt*)d_out : win));
+            }
+        }
+        if (!pair_t) {
+            msm_rc_bits<G><<<dim3(nbits * nslice, 1, Wr), 32, 0, st>>>(V, p.half, s, nbits, nslice, Us);
+            msm_rc_shift<G><<<dim3(nbits, 1, Wr), 32, 0, st>>>(Us, nbits, nslice, U);
+            msm_rc_final<G><<<Wr, 32, 0, st>>>(U, nbits, p.table ? (Pt*)d_out : win);
+        }
         ctx->launches += 5;
         if (!p.table) {
             msm_horner<G><<<1, 32, 0, st>>>(win, p.W, p.c, (Pt*)d_out);

@@ -77,6 +77,7 @@ unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by 
  *   "g2_pair"         G2 accumulate: 2 = one point per lane pair, lazy operand forms (default), 1 = strict forms,
  *                     3 = lazy + out-of-line products, 0 = one thread per point
  *   "finalize_chunks" 1 = stitch chunk partial sums with one thread per chunk edge (default), 0 = one per bucket
+ *   "pair_tail"       1 = the latency-bound last stages of the G2 bucket reduction with one point per lane pair (default)
  *   "split_chains"    1 = a multi-device context shares the first two transforms of the three evaluation vectors out over its
  *                     devices (default); 0 = every device runs all of them
  *   "finalize_big_seg" 1 = buckets spanning many chunks (the "scalar == 1" bucket of 0/1-heavy witnesses) summed in two levels,

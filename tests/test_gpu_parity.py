@@ -361,15 +361,15 @@ def test_msm_g2_lane_pair_full_addition(ctx):
         for window, chunk in ((11, 1), (12, 2), (0, 3), (14, 0)):
             if window:
                 tabled.precompute(window)
-            for pr in (1, 0):
-                ctx.set_option("pair_reduce", pr); ctx.set_option("chunk", chunk); ctx.set_option("window", window)
+            for pr, pt in ((1, 1), (1, 0), (0, 0)):        # lane-pair stage A + tail, stage A only, one thread per point
+                ctx.set_option("pair_reduce", pr); ctx.set_option("pair_tail", pt); ctx.set_option("chunk", chunk); ctx.set_option("window", window)
                 got, ginf = ctx.msm_g2(bases, inf, s)
-                assert ginf == winf and np.array_equal(got, want), (window, chunk, pr, "plain")
+                assert ginf == winf and np.array_equal(got, want), (window, chunk, pr, pt, "plain")
                 if window:
                     got, ginf = tabled.msm(s)
-                    assert ginf == winf and np.array_equal(got, want), (window, chunk, pr, "tables")
+                    assert ginf == winf and np.array_equal(got, want), (window, chunk, pr, pt, "tables")
     finally:
-        ctx.set_option("pair_reduce", PAIR_REDUCE_DEFAULT); ctx.set_option("chunk", 0); ctx.set_option("window", 0)
+        ctx.set_option("pair_reduce", PAIR_REDUCE_DEFAULT); ctx.set_option("pair_tail", 1); ctx.set_option("chunk", 0); ctx.set_option("window", 0)
         tabled.free()
 
 
