@@ -231,7 +231,7 @@ def host_cpu():
     return model, os.cpu_count() or 1
 
 
-def cpu_prove(log_m, steps, warmup, budget_s, flavour="field"):
+def cpu_prove(log_m, steps, warmup, budget_s, flavour="field", ref_phases=False):
     """Times the CPU implementation of the path on the host cores ON THE BENCHMARK'S OWN INSTANCE (the 2^log_m-constraint
     R1CS, no extrapolation), key generation and key parsing excluded: every step is one whole prove, the scope of the
     reference's "Call to r1cs_gg_ppzksnark_zok_prover" block (...zok.tcc:454-544).
@@ -272,14 +272,17 @@ def cpu_prove(log_m, steps, warmup, budget_s, flavour="field"):
             (len(times), log_m, "0/1-witness" if flavour == "binary" else "synthetic", wu,
              "oracle/_ref/ref_prove = the reference's own prover templates, alt_bn128 build (not the reference's default mcl curve code), -O3 -march=x86-64-v3"
              if use_ref else "oracle port", cores, model))
-    return dict(times=times, warmup=wu, threads=cores, kind=kind, cpu=model, desc=desc)
+    phases = None
+    if use_ref and ref_phases:
+        phases = orc_ref.prove_phases(circ, w, key, repeats=2, threads=cores)
+    return dict(times=times, warmup=wu, threads=cores, kind=kind, cpu=model, desc=desc, phases=phases)
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_prove(args.log_m, args.steps, args.warmup, args.cpu_budget_s, args.flavour)
+    r = cpu_prove(args.log_m, args.steps, args.warmup, args.cpu_budget_s, args.flavour, ref_phases=args.ref_phases)
     times = r["times"]
     mean_s, med_s = float(np.mean(times)), float(np.median(times))
     value = 1.0 / mean_s
@@ -293,6 +296,8 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "proofs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if r["phases"]:
+        line["phases_reference_blocks_ms"] = r["phases"]       # the reference's own enter_block timers, mean of 2 extra proves
     print(json.dumps(line))
 
 
@@ -528,6 +533,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": 64 + 128 + 64 + 3 * 4},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "phases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" not in k},
+        "phases_reference_blocks_ms": {k: round(v, 4) for k, v in eb.host.phases_as_reference_blocks(mean).items()},
         "msm_subphases_ms": {k: round(v, 4) for k, v in sorted(mean.items()) if "@" in k},
         "msm_kernels": kernels, "verified_in_the_exponent": verified,
     }
@@ -553,6 +559,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="both", choices=["both", "shard", "replicas"])
     ap.add_argument("--cpu-budget-s", type=float, default=200.0, help="--impl reference: bound on the summed prover time")
+    ap.add_argument("--ref-phases", action="store_true", help="--impl reference: also report the reference's own block timers")
     ap.add_argument("--flavour", default="field", choices=["field", "binary"],
                     help="R1CS generator: r1cs_examples.tcc:25-93 (uniform field witness) or :100-157 (0/1 witness)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

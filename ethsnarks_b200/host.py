@@ -207,6 +207,24 @@ def generate_r1cs_example_with_binary_input(num_constraints, num_inputs, seed=1)
     return Protoboard(cs, bits)
 
 
+# The reference prover's own timing blocks (libff::enter_block names, src/r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.tcc:454-544) and
+# the library phases (b200_timing_get names) each of them covers, so that CPU and GPU phase tables can be laid side by side.
+REFERENCE_BLOCKS = {
+    "Call to r1cs_gg_ppzksnark_zok_prover": ("prove.total",),
+    "Compute the polynomial H": ("h2d.witness", "witness_eval", "h_chain", "h_chain.front", "h_chain.back"),
+    "Compute evaluation to A-query": ("msm.A",),
+    "Compute evaluation to B-query": ("msm.B_g2",),
+    "Compute evaluation to H-query": ("msm.H",),
+    "Compute evaluation to L-query": ("msm.L",),
+    "Compute the proof": ("msm.A", "msm.B_g2", "msm.H", "msm.L", "finish", "combine"),
+}
+
+
+def phases_as_reference_blocks(phases_ms):
+    """{library phase: ms} (serialised phases) -> {reference block name: ms}"""
+    return {blk: float(sum(phases_ms.get(n, 0.0) for n in names)) for blk, names in REFERENCE_BLOCKS.items()}
+
+
 def _hex(x):
     return "0x%x" % x
 

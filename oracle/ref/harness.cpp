@@ -131,6 +131,10 @@ int main(int argc, char** argv) {
     ctx.aA.resize(m + 1); ctx.aB.resize(m + 1); ctx.aH.resize(m + 1);
     ctx.scratch_exponents.resize(m + nv + 8);
 
+    // REF_PHASES=1: keep libff's block timers running (enter_block / leave_block, profiling.cpp) and print the mean time of the
+    // prover's own blocks, so that the GPU phase table can be laid beside the reference's under the reference's block names
+    const bool want_phases = getenv("REF_PHASES") != nullptr;
+    if (want_phases) { libff::inhibit_profiling_counters = false; libff::clear_profiling_counters(); }
     double best = 1e30;
     std::vector<double> times;
     double used = 0;
@@ -143,6 +147,19 @@ int main(int argc, char** argv) {
         times.push_back(dt);
         used += dt;
         if (budget > 0 && used > budget && i + 1 >= min_repeats) break;
+    }
+    if (want_phases) {
+        const char* blocks[] = {"Call to r1cs_gg_ppzksnark_zok_prover", "Compute the polynomial H", "Compute the proof", "Compute evaluation to A-query",
+                                "Compute evaluation to B-query", "Compute evaluation to H-query", "Compute evaluation to L-query"};
+        std::cerr << "{";
+        bool first = true;
+        for (const char* b : blocks) {
+            auto it = libff::cumulative_times.find(b);
+            if (it == libff::cumulative_times.end()) continue;
+            std::cerr << (first ? "" : ", ") << "\"" << b << "\": " << (double)it->second * 1e-6 / (double)times.size();
+            first = false;
+        }
+        std::cerr << "}\n";
     }
     std::ofstream out(argv[2], std::ios::binary);
     auto A = proof.g_A; A.to_affine_coordinates();

@@ -58,6 +58,19 @@ def write_problem(path, circ, w, pk_alt_nozk_bytes):
         f.write(pk_alt_nozk_bytes)
 
 
+def prove_phases(circ, w, key, repeats=2, threads=None):
+    """mean milliseconds of the reference prover's own enter_block/leave_block blocks (…zok.tcc:454-544) over `repeats` proves"""
+    import json
+    with tempfile.TemporaryDirectory() as d:
+        prob, out = os.path.join(d, "problem.bin"), os.path.join(d, "out.bin")
+        write_problem(prob, circ, w, key.serialize(orc.FMT_ALT_NOZK))
+        env = dict(os.environ, REF_PHASES="1")
+        if threads:
+            env["OMP_NUM_THREADS"] = str(threads)
+        res = subprocess.run([REF_BIN, prob, out, str(repeats)], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
+    return json.loads([l for l in res.stderr.splitlines() if l.startswith("{")][-1])
+
+
 def prove(circ, w, key, repeats=1, threads=None, all_times=False, budget_s=None, min_repeats=None):
     """returns ((A, B, C, inf) in the oracle's layout, H coefficients (m, 4) Montgomery, seconds); seconds = the fastest
     repeat, or with all_times the list of every repeat's duration in call order"""
