@@ -27,6 +27,25 @@ template <typename T> static void rd(std::istream& in, T& v) { in.read((char*)&v
 static FieldT rd_fr(std::istream& in) { FieldT f; in.read((char*)f.mont_repr.data, 32); return f; }
 template <typename F> static void wr_std(std::ostream& out, const F& f) { auto b = f.as_bigint(); out.write((const char*)b.data, 32); }
 
+// --msm: n bases k_i * G by the reference's fixed-base machinery, then `reps` timed calls of its multi_exp
+template <typename G>
+static void msm_times(size_t n, const std::vector<FieldT>& ks, const std::vector<FieldT>& ss, int reps, int mix, std::vector<double>& times) {
+    const size_t sb = FieldT::size_in_bits();
+    libsnark::Config config;
+    std::vector<libff::bigint<FieldT::num_limbs>> scratch;
+    const size_t window = libff::get_exp_window_size<G>(n);
+    auto table = libff::get_window_table<G>(sb, window, G::one());
+    std::vector<G> bases = libff::batch_exp<G, FieldT>(sb, window, table, ks);
+    libff::batch_to_special<G>(bases);
+    for (int r = 0; r < reps; ++r) {
+        auto t0 = std::chrono::steady_clock::now();
+        G res = mix ? libff::multi_exp_with_mixed_addition<G, FieldT, libff::multi_exp_method_BDLO12>(bases.begin(), bases.end(), ss.begin(), ss.end(), scratch, config)
+                    : libff::multi_exp<G, FieldT, libff::multi_exp_method_BDLO12>(bases.begin(), bases.end(), ss.begin(), ss.end(), scratch, config);
+        times.push_back(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+        if (res.is_zero()) std::cerr << "zero result\n";
+    }
+}
+
 int main(int argc, char** argv) {
     if (argc == 4 && std::string(argv[1]) == "--roundtrip-full") {
         // pins the byte layout of the UN-STRIPPED key: the reference's own operator>> for r1cs_gg_ppzksnark_zok_proving_key
@@ -51,30 +70,14 @@ int main(int argc, char** argv) {
         ppT::init_public_params();
         libff::inhibit_profiling_info = true;
         libff::inhibit_profiling_counters = true;
-        const size_t n = (size_t)1 << logn, sb = FieldT::size_in_bits();
+        const size_t n = (size_t)1 << logn;
         std::vector<FieldT> ks(n), ss(n);
         for (size_t i = 0; i < n; ++i) {
             ks[i] = libff::SHA512_rng<FieldT>(((uint64_t)1 << 40) + i);
             ss[i] = (mix && i % 10) ? ((i / 10 + i) & 1 ? FieldT::one() : FieldT::zero()) : libff::SHA512_rng<FieldT>(i);
         }
-        libsnark::Config config;
-        std::vector<libff::bigint<FieldT::num_limbs>> scratch;
         std::vector<double> times;
-        auto run = [&](auto one) {
-            typedef decltype(one) G;
-            const size_t window = libff::get_exp_window_size<G>(n);
-            auto table = libff::get_window_table<G>(sb, window, one);
-            std::vector<G> bases = libff::batch_exp<G, FieldT>(sb, window, table, ks);
-            libff::batch_to_special<G>(bases);
-            for (int r = 0; r < reps; ++r) {
-                auto t0 = std::chrono::steady_clock::now();
-                G res = mix ? libff::multi_exp_with_mixed_addition<G, FieldT, libff::multi_exp_method_BDLO12>(bases.begin(), bases.end(), ss.begin(), ss.end(), scratch, config)
-                            : libff::multi_exp<G, FieldT, libff::multi_exp_method_BDLO12>(bases.begin(), bases.end(), ss.begin(), ss.end(), scratch, config);
-                times.push_back(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
-                if (res.is_zero()) std::cerr << "zero result\n";
-            }
-        };
-        if (group == 1) run(libff::G1<ppT>::one()); else run(libff::G2<ppT>::one());
+        if (group == 1) msm_times<libff::G1<ppT>>(n, ks, ss, reps, mix, times); else msm_times<libff::G2<ppT>>(n, ks, ss, reps, mix, times);
         std::cout << "{\"group\": \"G" << group << "\", \"log_n\": " << logn << ", \"mix\": " << mix << ", \"threads\": " << omp_get_max_threads()
                   << ", \"seconds\": [";
         for (size_t i = 0; i < times.size(); ++i) std::cout << (i ? ", " : "") << times[i];
