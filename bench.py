@@ -1,19 +1,21 @@
 #!/usr/bin/env python
 """bench.py — Groth16 prove throughput on synthetic R1CS (BASELINE.json metric), one process per GPU.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--log-m 20] [--impl ours|reference] [--mode both|shard|replicas]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--log-m 20] [--flavour field|binary] [--impl ours|reference]
+                  [--mode both|shard|replicas] [--staged 0|1]
 
 A "step" is one full prove (witness-times-R1CS, the 7-NTT H chain, the A / B(G2) / H / L multi-scalar
-multiplications, the final additions) of the synthetic 2^log_m-constraint R1CS of r1cs_examples.tcc:25-93 against a
-device-resident synthetic proving key of the matching shape.  `value` is measured with the witness already in HBM,
-`e2e` through the host-buffer C-ABI call (pinned witness H2D and proof D2H inside the timed region).
-With N > 1 (torchrun) the headline `value` is N ranks proving independent witnesses against a resident key each
-("replicas", weak scaling: proofs are independent units, no data-path collective).  The same run also measures the
-north-star's MSM split and reports it under "sharded": every query of the key split 1/N per rank, each rank proves its
-slice, the three partial sums per rank (35 x 8 B) are all-gathered over NCCL and rank 0 combines (strong scaling of ONE
-proof's latency).  `--mode shard` / `--mode replicas` run one arrangement only.
-`--impl reference` times the CPU implementation of the same path (oracle/_ref, the reference's own prover built from its sources;
-else the oracle port) instead.
+multiplications, the final additions) of the synthetic 2^log_m-constraint R1CS of r1cs_examples.tcc:25-93 (or, with
+--flavour binary, the 0/1-witness one of :100-157) against a device-resident synthetic proving key of the matching shape.
+`value` is measured with the witnesses already in HBM, `e2e` through the host-buffer C-ABI call (pinned witness H2D and proof
+D2H inside the timed region); the timed loops alternate between two distinct witnesses of the circuit.
+With N > 1 (torchrun) the headline is ONE proof over a key sharded 1/N per rank ("scaling": "strong"): every rank proves its
+slice of every query, the ranks share the three transform chains (each vector of coset evaluations is computed by one rank and
+broadcast over NCCL), the 256-byte partial sums are all-gathered on the device and rank 0 combines them; the N-rank proof is
+compared byte for byte with the one-GPU proof inside the run.  The other arrangement - N independent replicas, weak scaling,
+no collective - is measured in the same run and reported under "replicas".  `--mode shard` / `--mode replicas` run one only.
+`--impl reference` times the CPU implementation of the same path (oracle/_ref/ref_prove, the reference's own prover built from
+its sources; else the oracle port) on the benchmark's own instance, every step one whole prove on all host threads.
 """
 import argparse
 import json
@@ -371,13 +373,30 @@ def run_ours(args):
     w_dev = torch.from_numpy(witness.view(np.int64)).to(dev)            # resident witness (`value`)
     w_pin = torch.from_numpy(witness.view(np.int64)).pin_memory()       # pinned host witness (`e2e`)
 
+    # proofs/s is defined over DISTINCT witnesses: the timed loops alternate between two satisfying assignments
+    # of the same circuit (the generator's seeds changed); above 2^22 the second one is skipped to bound the set-up time
+    w_devs, w_pins = [w_dev], [w_pin]
+    if args.log_m <= 22 and args.flavour == "field":      # (the 0/1 generator's seed also changes the circuit: one witness there)
+        nc2 = (1 << args.log_m) - 2
+        pb2 = eb.generate_r1cs_example_with_field_input(nc2, 1, seed_a=2, seed_b=3)
+        w2 = eb.host.fr_to_mont(pb2.values)
+        assert w2.shape == witness.shape and not np.array_equal(w2, witness)
+        w_devs.append(torch.from_numpy(w2.view(np.int64)).to(dev))
+        w_pins.append(torch.from_numpy(w2.view(np.int64)).pin_memory())
+        del pb2
+
     sharded_prove = ShardedProver(key, world, rank, stream, dev, staged=bool(args.staged)) if shard else None
 
     def step(wptr):
         return sharded_prove(wptr) if shard else key.prove(wptr)
 
-    def timed(wptr, steps, collect):
-        return timed_steps(lambda: step(wptr), steps, collect)
+    def timed(bufs, steps, collect):
+        it = [0]
+
+        def one():
+            step(bufs[it[0] % len(bufs)].data_ptr())
+            it[0] += 1
+        return timed_steps(one, steps, collect)
 
     # pipelined proving: a second prove slot on the same resident key (b200_key_attach), driven from a second host thread,
     # so the start-up (digits + sort) and the latency-bound tail of one proof overlap the next proof's accumulate kernels
@@ -427,7 +446,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     phases = []
-    ms_lat, launches = timed(w_dev.data_ptr(), args.steps, None)            # one proof at a time: latency
+    ms_lat, launches = timed(w_devs, args.steps, None)                      # one proof at a time: latency
     ms_dev, ms_e2e = ms_lat, None
     if len(slots) > 1:
         # each slot proves from its own witness buffer (same values: the MSM/NTT cost does not depend on them)
@@ -437,13 +456,14 @@ def run_ours(args):
         run_steps([w_pin.data_ptr(), w2_pin.data_ptr()], len(slots))
         ms_e2e, _ = timed_pipelined([w_pin.data_ptr(), w2_pin.data_ptr()], args.steps)
     else:
-        step(w_pin.data_ptr())
-        ms_e2e, _ = timed(w_pin.data_ptr(), args.steps, None)
+        for wp in w_pins:
+            step(wp.data_ptr())
+        ms_e2e, _ = timed(w_pins, args.steps, None)
     # per-kernel durations for the roofline: the same steps with the MSM lanes serialised, so that each kernel's
     # CUDA-event bracket on its launching stream contains that kernel alone
     ctx.set_option("overlap", 0)
     step(w_dev.data_ptr())
-    timed(w_dev.data_ptr(), min(args.steps, 3), phases)
+    timed(w_devs, min(args.steps, 3), phases)
     ctx.set_option("overlap", 1)
     clocks = sampler.stop() if rank == 0 else None
 
@@ -527,7 +547,7 @@ def run_ours(args):
                    "parallelism": ("ONE proof over a key sharded 1/%d per GPU%s; 256-byte partial sums all-gathered over NCCL on the device" % (world, ", transform chains shared out and broadcast over NCCL" if args.staged else "")) if shard else
                                   (("%d independent replicas" % world if world > 1 else "single GPU") +
                                    (", %d proofs in flight per GPU on one resident key" % len(slots) if len(slots) > 1 else "")),
-                   "l2": "inputs larger than L2 (key + sort buffers >> 126 MB per prove)", "r_s": "0,0 (reference no-ZK prover)"},
+                   "l2": "inputs larger than L2 (key + sort buffers >> 126 MB per prove)", "distinct_witnesses": len(w_devs), "r_s": "0,0 (reference no-ZK prover)"},
         "latency_ms": ms_lat / args.steps, "proofs_in_flight": len(slots),
         "e2e": {"value": e2e, "unit": "proofs/s", "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": int(nbytes_w),
                 "d2h_bytes_per_step": 64 + 128 + 64 + 3 * 4},

@@ -25,6 +25,9 @@ struct b200_key {
     b200_ctx* ctx = nullptr;
     bool full = false;          // has the B query in G1 (r,s mode possible)
     bool owns_bases = true;
+    int children = 0;           // prove slots attached to this key (b200_key_attach) that are still alive
+    bool free_pending = false;  // b200_key_free was called while slots were alive: released when the last slot goes
+    b200_key* parent = nullptr; // of an attached slot
     bool attached = false;      // a second prove slot on a resident key: shares every read-only buffer, owns only d_w/d_a/d_b/d_c
     int rank = 0, world = 1;
     uint64_t domain_size = 0;   // num_variables + 1
@@ -450,6 +453,99 @@ static int key_load_one(b200_ctx* ctx, const void* bytes, size_t len, int fmt, i
         return (int)B200_OK;
     });
 }
+// Key file converters (host only, no device needed): the byte-level counterparts of the reference's pk_alt2mcl and pk_mcl2nozk
+// (src/export.cpp:330-408).  Any of the four reference layouts in, any out - except NOZK -> FULL, which would need the G1 half
+// of the B query and the zero entries of A that the stripped key no longer holds.  FULL -> NOZK drops the B query's G1 half
+// and the zero entries of the dense A query (…zok.hpp:218-230).
+int b200_key_convert(const void* bytes, size_t len, int fmt_in, int fmt_out, void* out, size_t cap, size_t* len_out) {
+    if (!bytes || !len_out || fmt_in < 0 || fmt_in > 3 || fmt_out < 0 || fmt_out > 3) return B200_ERR_ARG;
+    const bool in_full = fmt_in & 1, out_full = fmt_out & 1, out_alt = fmt_out >= 2;
+    if (!in_full && out_full) return B200_ERR_ARG;
+    try {
+        Reader rd{(const uint8_t*)bytes, (const uint8_t*)bytes + len, fmt_in >= 2};
+        std::string o;
+        o.reserve(len + len / 2);
+        static const uint64_t one[4] = {0xd35d438dc58f0d9dull, 0x0a78eb28f5c70b3dull, 0x666ea36f7879462cull, 0x0e0a77c19a07df2full};   // R mod q
+        auto put = [&](int group, const uint8_t* p) {       // p: affine Montgomery, all-zero = infinity
+            const size_t ab = group == 1 ? 64 : 128;
+            bool inf = true;
+            for (size_t i = 0; i < ab; ++i) if (p[i]) { inf = false; break; }
+            o.push_back(inf ? '1' : '0');
+            if (out_alt) {
+                if (!inf) { o.append((const char*)p, ab); return; }
+                o.append(ab / 2, '\0');                                   // x = 0
+                o.append((const char*)one, 32);                           // y = 1 (G2: 1 + 0 u)
+                if (group == 2) o.append(32, '\0');
+            } else {
+                if (inf) { o.append(ab + ab / 2, '\0'); return; }         // mcl: x, y, z all zero
+                o.append((const char*)p, ab);
+                o.append((const char*)one, 32);                           // z = 1
+                if (group == 2) o.append(32, '\0');
+            }
+        };
+        auto num = [&](uint64_t v) { o += std::to_string(v); o.push_back('\n'); };
+        uint8_t pt[128], pt1[64];
+        for (int g : {1, 1, 2, 1, 2}) { rd.point(g, pt); put(g, pt); }          // alpha_g1 beta_g1 beta_g2 delta_g1 delta_g2
+        // A query
+        uint64_t domain = 0;
+        if (in_full) {
+            const uint64_t n = rd.number();
+            domain = n;
+            if (out_full) {
+                num(n);
+                for (uint64_t i = 0; i < n; ++i) { rd.point(1, pt); put(1, pt); }
+            } else {
+                std::vector<uint64_t> idx;
+                std::string vals;
+                std::swap(o, vals);                                             // collect the kept points in `vals`
+                for (uint64_t i = 0; i < n; ++i) {
+                    rd.point(1, pt);
+                    bool inf = true;
+                    for (int b = 0; b < 64; ++b) if (pt[b]) { inf = false; break; }
+                    if (!inf) { idx.push_back(i); put(1, pt); }
+                }
+                std::swap(o, vals);
+                num(n); num(idx.size());
+                for (uint64_t i : idx) num(i);
+                num(idx.size());
+                o += vals;
+            }
+        } else {
+            domain = rd.number();
+            const uint64_t n_idx = rd.number();
+            num(domain); num(n_idx);
+            for (uint64_t i = 0; i < n_idx; ++i) num(rd.number());
+            const uint64_t n_val = rd.number();
+            if (n_val != n_idx) throw std::domain_error("proving key: sparse vector with different index and value counts");
+            num(n_val);
+            for (uint64_t i = 0; i < n_val; ++i) { rd.point(1, pt); put(1, pt); }
+        }
+        // B query: sparse in every layout
+        {
+            const uint64_t ds = rd.number(), n_idx = rd.number();
+            num(ds); num(n_idx);
+            for (uint64_t i = 0; i < n_idx; ++i) num(rd.number());
+            const uint64_t n_val = rd.number();
+            if (n_val != n_idx) throw std::domain_error("proving key: sparse vector with different index and value counts");
+            num(n_val);
+            for (uint64_t i = 0; i < n_val; ++i) {
+                rd.point(2, pt); put(2, pt);
+                if (in_full) { rd.point(1, pt1); if (out_full) put(1, pt1); }
+            }
+        }
+        for (int q = 0; q < 2; ++q) {                                            // H, L
+            const uint64_t n = rd.number();
+            num(n);
+            for (uint64_t i = 0; i < n; ++i) { rd.point(1, pt); put(1, pt); }
+        }
+        *len_out = o.size();
+        if (out && cap >= o.size()) memcpy(out, o.data(), o.size());
+        return B200_OK;
+    } catch (const std::exception&) {
+        return B200_ERR_FORMAT;
+    }
+}
+
 int b200_key_export(b200_key* k, void* buf, size_t cap, size_t* len_out) {
     if (!k || !len_out) return B200_ERR_ARG;
     b200_ctx* ctx = k->ctx;
@@ -576,10 +672,14 @@ int b200_key_attach(b200_key* key, b200_ctx* ctx, b200_key** out) {
     if (!key->has_circuit) { ctx->last_error = "key_attach before circuit_load"; return B200_ERR_STATE; }
     if (ctx->device != key->ctx->device) { ctx->last_error = "key_attach: the context is on another device"; return B200_ERR_ARG; }
     return Guard{ctx}.run([&] {
-        std::unique_ptr<b200_key, void (*)(b200_key*)> k(new b200_key(*key), key_release);
+        std::vector<uint8_t> keep_h;
+        keep_h.swap(key->H_host);                           // do not copy the host copy of the H query into the slot
+        std::unique_ptr<b200_key, void (*)(b200_key*)> k(nullptr, key_release);
+        try { k.reset(new b200_key(*key)); } catch (...) { keep_h.swap(key->H_host); throw; }
+        keep_h.swap(key->H_host);
         k->attached = true;
         k->ctx = ctx;
-        k->H_host.clear();
+        k->parent = key; k->children = 0; k->free_pending = false;
         k->d_w = k->d_a = k->d_b = k->d_c = k->d_h = nullptr;
         B200_CUDA_CHECK(cudaMalloc(&k->d_w, (k->nv + 1) * 32));
         B200_CUDA_CHECK(cudaMalloc(&k->d_a, k->m * 32));
@@ -588,15 +688,28 @@ int b200_key_attach(b200_key* key, b200_ctx* ctx, b200_key** out) {
         B200_CUDA_CHECK(cudaMemset(k->d_a, 0, k->m * 32));
         B200_CUDA_CHECK(cudaMemset(k->d_b, 0, k->m * 32));
         B200_CUDA_CHECK(cudaMemset(k->d_c, 0, k->m * 32));
+        key->children++;
         *out = k.release();
         return (int)B200_OK;
     });
 }
 
+// A key with live attached slots is not released under them: the release is deferred until the last slot is freed.
 void b200_key_free(b200_key* key) {
     if (!key) return;
     cudaSetDevice(key->ctx->device);
     cudaStreamSynchronize(key->ctx->stream);
+    if (key->attached) {
+        b200_key* parent = key->parent;
+        key_release(key);
+        if (parent && --parent->children == 0 && parent->free_pending) {
+            cudaSetDevice(parent->ctx->device);
+            cudaStreamSynchronize(parent->ctx->stream);
+            key_release(parent);
+        }
+        return;
+    }
+    if (key->children > 0) { key->free_pending = true; return; }
     key_release(key);
 }
 int b200_key_info(b200_key* k, uint64_t out[8]) {

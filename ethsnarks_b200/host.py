@@ -229,13 +229,17 @@ def _hex(x):
     return "0x%x" % x
 
 
-def proof_to_json(proof, primary_input):
-    """src/export.cpp:56-121: affine hex, G2 as [x.c1, x.c0], [y.c1, y.c0]; byte-for-byte the reference's layout."""
+def proof_to_json(proof, primary_input, curve="alt"):
+    """src/export.cpp:56-121: affine hex, G2 as [x.c1, x.c0], [y.c1, y.c0]; byte-for-byte the reference's layout.
+    The one place where the string depends on the reference's curve build is a proof point at infinity (no real proof has
+    one): the CURVE_ALT_BN128 branch prints libff's zero (0, 1) (alt_bn128_g1.cpp to_affine_coordinates), the default
+    CURVE_MCL_BN128 branch prints the cleared mcl point, (0, 0) - `curve` selects which."""
     A, B, Cc, inf = proof
     a = limbs_to_ints(A); b = limbs_to_ints(B); c = limbs_to_ints(Cc)
-    if inf[0]: a = [0, 1]
-    if inf[1]: b = [0, 0, 1, 0]
-    if inf[2]: c = [0, 1]
+    y0 = 1 if curve == "alt" else 0
+    if inf[0]: a = [0, y0]
+    if inf[1]: b = [0, 0, y0, 0]
+    if inf[2]: c = [0, y0]
     s = "{\n"
     s += ' "A" :["%s", "%s"],\n' % (_hex(a[0]), _hex(a[1]))
     s += ' "B"  :[["%s", "%s"],\n ["%s", "%s"]],\n' % (_hex(b[1]), _hex(b[0]), _hex(b[3]), _hex(b[2]))
@@ -270,6 +274,61 @@ def vk_to_json(vk):
     s += ' "delta" :[' + g2(vk["delta"]) + "],\n"
     s += '"gammaABC" :[' + ",".join("[" + g1(p) + "]" for p in vk["gammaABC"]) + "]}"
     return s
+
+
+def pk_bellman2ethsnarks(bellman_json, alt=True):
+    """pk_bellman2ethsnarks (src/export.cpp:267-328): a bellman-style proving key as JSON - "A", "B1", "B2", "C", "hExps" lists of
+    Jacobian points ([x, y, z] decimal strings; G2 coordinates as [c0, c1] pairs) and vk_alfa_1, vk_beta_1/2, vk_delta_1/2 - to the
+    bytes of the reference's stripped proving key (B200_FMT_ALT_NOZK, or MCL_NOZK with alt=False), which b200_key_load reads.
+    As the reference does: B entries whose G1 half is zero are dropped, the first two "C" entries are skipped (:305), zero
+    entries of A are dropped by the _nozk conversion (…zok.hpp:218-230), points are written normalised."""
+    import json as _json
+    d = _json.loads(bellman_json) if isinstance(bellman_json, (str, bytes)) else bellman_json
+    q = Q_MOD
+    one = MONT_R % q
+
+    def fq(x):
+        return ((int(x) % q) * MONT_R % q).to_bytes(32, "little")
+
+    def g1(p):                                     # Jacobian (X, Y, Z) -> affine bytes, None for zero
+        x, y, z = (int(v) % q for v in p)
+        if z == 0:
+            return None
+        zi = pow(z, -1, q)
+        return fq(x * zi * zi % q) + fq(y * zi * zi * zi % q)
+
+    def g2(p):                                     # Fq2 = c0 + c1 u, u^2 = -1
+        (x0, x1), (y0, y1), (z0, z1) = ((int(a) % q, int(b) % q) for a, b in p)
+        if z0 == 0 and z1 == 0:
+            return None
+        mul = lambda a, b: ((a[0] * b[0] - a[1] * b[1]) % q, (a[0] * b[1] + a[1] * b[0]) % q)
+        n = pow((z0 * z0 + z1 * z1) % q, -1, q)
+        zi = (z0 * n % q, (-z1) * n % q)
+        zi2 = mul(zi, zi)
+        zi3 = mul(zi2, zi)
+        X, Y = mul((x0, x1), zi2), mul((y0, y1), zi3)
+        return fq(X[0]) + fq(X[1]) + fq(Y[0]) + fq(Y[1])
+
+    def put(pt, nbytes):
+        if alt:
+            return (b"0" + pt) if pt is not None else (b"1" + bytes(nbytes // 2) + one.to_bytes(32, "little") + bytes(nbytes // 2 - 32))
+        return (b"0" + pt + one.to_bytes(32, "little") + bytes(nbytes // 2 - 32)) if pt is not None else (b"1" + bytes(nbytes + nbytes // 2))
+
+    out = [put(g1(d["vk_alfa_1"]), 64), put(g1(d["vk_beta_1"]), 64), put(g2(d["vk_beta_2"]), 128), put(g1(d["vk_delta_1"]), 64),
+           put(g2(d["vk_delta_2"]), 128)]
+    A = [g1(p) for p in d["A"]]
+    keepA = [i for i, p in enumerate(A) if p is not None]
+    out.append(("%d\n%d\n" % (len(A), len(keepA))).encode() + b"".join(b"%d\n" % i for i in keepA) + b"%d\n" % len(keepA))
+    out += [put(A[i], 64) for i in keepA]
+    keepB = [i for i, p in enumerate(d["B1"]) if g1(p) is not None]
+    out.append(("%d\n%d\n" % (len(A), len(keepB))).encode() + b"".join(b"%d\n" % i for i in keepB) + b"%d\n" % len(keepB))
+    out += [put(g2(d["B2"][i]), 128) for i in keepB]
+    out.append(b"%d\n" % len(d["hExps"]))
+    out += [put(g1(p), 64) for p in d["hExps"]]
+    L = d["C"][2:]
+    out.append(b"%d\n" % len(L))
+    out += [put(g1(p), 64) for p in L]
+    return b"".join(out)
 
 
 def generate_keypair(ctx, pb, toxic, full=False):

@@ -28,7 +28,7 @@ SYMBOLS = [
     "b200_bases_download", "b200_bases_count", "b200_bases_free", "b200_msm", "b200_key_load", "b200_key_load_sharded",
     "b200_key_from_bases", "b200_key_free", "b200_key_info", "b200_circuit_load", "b200_prove", "b200_h",
     "b200_witness_eval", "b200_prove_partial", "b200_proof_combine", "b200_imad_peak", "b200_key_set_shard", "b200_bases_precompute", "b200_key_attach", "b200_key_export",
-    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc", "b200_device_count", "b200_chain_owner", "b200_key_buffers", "b200_prove_partial_stage1", "b200_prove_partial_stage2", "b200_circuit_load_instanced", "b200_prove_partial_dev", "b200_proof_combine_dev",
+    "b200_generate_key", "b200_g1_sum", "b200_g2_sum", "b200_g1_sum_noalloc", "b200_device_count", "b200_key_convert", "b200_chain_owner", "b200_key_buffers", "b200_prove_partial_stage1", "b200_prove_partial_stage2", "b200_circuit_load_instanced", "b200_prove_partial_dev", "b200_proof_combine_dev",
 ]
 
 
@@ -46,6 +46,21 @@ class B200Error(RuntimeError):
 
 
 _lib = None
+
+
+def key_convert(pk_bytes, fmt_in, fmt_out):
+    """b200_key_convert: reference key bytes from one of the four layouts to another (pk_alt2mcl / pk_mcl2nozk, export.cpp:330-408);
+    host only - works without a GPU"""
+    lib = load()
+    n = C.c_size_t()
+    rc = lib.b200_key_convert(pk_bytes, C.c_size_t(len(pk_bytes)), fmt_in, fmt_out, None, C.c_size_t(0), C.byref(n))
+    if rc:
+        raise B200Error("key_convert: " + lib.b200_strerror(rc).decode())
+    buf = C.create_string_buffer(n.value)
+    rc = lib.b200_key_convert(pk_bytes, C.c_size_t(len(pk_bytes)), fmt_in, fmt_out, buf, n, C.byref(n))
+    if rc:
+        raise B200Error("key_convert: " + lib.b200_strerror(rc).decode())
+    return buf.raw[:n.value]
 
 
 def chain_owner(chain, world):

@@ -142,6 +142,10 @@ int b200_msm(b200_ctx* ctx, b200_bases* bases, const uint64_t* scalars_mont, siz
 
 /* ---- the prove path ---- */
 int b200_key_load(b200_ctx* ctx, const void* pk_bytes, size_t len, int fmt, b200_key** out);
+/* Key file converters, host only (no device, no context): the byte-level counterparts of the reference's pk_alt2mcl and
+ * pk_mcl2nozk (src/export.cpp:330-408).  Any B200_FMT_{MCL,ALT}_{NOZK,FULL} layout in, any out, except NOZK -> FULL (the stripped
+ * key no longer holds what the full one needs: B200_ERR_ARG).  *len_out = bytes needed; out may be NULL / short for a size query. */
+int b200_key_convert(const void* pk_bytes, size_t len, int fmt_in, int fmt_out, void* out, size_t cap, size_t* len_out);
 /* keep only this rank's 1/world slice of every query (multi-GPU: one process per GPU, see b200_prove_partial) */
 int b200_key_load_sharded(b200_ctx* ctx, const void* pk_bytes, size_t len, int fmt, int rank, int world, b200_key** out);
 /* a key assembled from resident base sets (synthetic keys for benchmarks); takes ownership of nothing, copies nothing:

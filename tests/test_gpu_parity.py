@@ -800,7 +800,16 @@ def test_key_attach_second_prove_slot_and_handle_lifetimes(ctx):
     got = pk.prove(w)     # the parent key is untouched
     for g, e in zip(got, want):
         assert np.array_equal(np.asarray(g), np.asarray(e))
-    pk.free()
+    # freeing the parent at the C ABI while a slot is alive defers its release: the slot keeps proving from live memory
+    ctx4 = eb.Context(0)
+    slot2 = pk.attach(ctx4)
+    pk.ctx.lib.b200_key_free(pk.h)
+    pk.h = L.C.c_void_p()
+    pk._slots.clear()
+    for g, e in zip(slot2.prove(w), want):
+        assert np.array_equal(np.asarray(g), np.asarray(e))
+    slot2.free()          # last slot gone: the parent is released now
+    ctx4.close()
     ctx3 = eb.Context(0)
     orphan = _load(ctx3, circ, key, orc.FMT_MCL_NOZK, eb.FMT_MCL_NOZK)
     ctx3.close()

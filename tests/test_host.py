@@ -1,5 +1,6 @@
 """CPU tests of the host side: the C-ABI library loads and exports every declared symbol, the host mirror of the
 reference interface agrees with the oracle, and the N>1 sharding logic (gloo, world_size 2)."""
+import json
 import os
 import re
 import subprocess
@@ -116,3 +117,81 @@ def test_constraint_instances_flatten_like_the_reference():
     assert cs.is_satisfied(pb.values)
     pb.values[4] = (pb.values[4] + 1) % H.R_MOD
     assert not cs.is_satisfied(pb.values)
+
+
+def test_key_converters_match_the_oracle_serialisations():
+    """b200_key_convert (host only: pk_alt2mcl / pk_mcl2nozk, src/export.cpp:330-408) between the four reference layouts, each of
+    which the oracle writes from the same key; NOZK -> FULL is refused.  The ALT layouts are pinned on the reference's own
+    stream operators (tests/test_oracle.py)."""
+    from ethsnarks_b200 import lib as L
+    import orc
+    c = orc.Circuit.synth_binary(60, 3)
+    k = orc.Key(c)
+    fm = {L.FMT_MCL_NOZK: orc.FMT_MCL_NOZK, L.FMT_MCL_FULL: orc.FMT_MCL_FULL, L.FMT_ALT_NOZK: orc.FMT_ALT_NOZK, L.FMT_ALT_FULL: orc.FMT_ALT_FULL}
+    blobs = {f: k.serialize(o) for f, o in fm.items()}
+    for fi in fm:
+        for fo in fm:
+            if not (fi & 1) and (fo & 1):
+                with pytest.raises(L.B200Error):
+                    L.key_convert(blobs[fi], fi, fo)
+            else:
+                assert L.key_convert(blobs[fi], fi, fo) == blobs[fo], (fi, fo)
+    with pytest.raises(L.B200Error):
+        L.key_convert(blobs[L.FMT_ALT_FULL][:-7], L.FMT_ALT_FULL, L.FMT_MCL_NOZK)      # truncated
+
+
+def test_pk_bellman2ethsnarks_matches_the_oracle_key():
+    """host.pk_bellman2ethsnarks (src/export.cpp:267-328): an oracle key written out as a bellman-style JSON (Jacobian points with
+    random z, decimal strings) comes back as the bytes of the stripped reference key."""
+    import random
+    import orc
+    H = eb.host
+    rng = random.Random(3)
+    c = orc.Circuit.synth_binary(40, 2)
+    k = orc.Key(c)
+    full = k.serialize(orc.FMT_ALT_FULL)
+    q = H.Q_MOD
+    rinv = pow(H.MONT_R, -1, q)
+    pos = [0]
+
+    def take(n):
+        b = full[pos[0]:pos[0] + n]; pos[0] += n
+        return b
+
+    def num():
+        e = full.index(b"\n", pos[0]); v = int(full[pos[0]:e]); pos[0] = e + 1
+        return v
+
+    def fqs(b):
+        return [int.from_bytes(b[i:i + 32], "little") * rinv % q for i in range(0, len(b), 32)]
+
+    def g1():
+        inf = take(1) == b"1"; x, y = fqs(take(64))
+        if inf:
+            return ["0", "1", "0"]
+        z = rng.randrange(1, q)
+        return [str(x * z * z % q), str(y * z * z * z % q), str(z)]
+
+    def g2():
+        inf = take(1) == b"1"; x0, x1, y0, y1 = fqs(take(128))
+        if inf:
+            return [["0", "0"], ["1", "0"], ["0", "0"]]
+        z = rng.randrange(1, q)                                        # z = z + 0 u keeps the arithmetic in Fq
+        return [[str(x0 * z * z % q), str(x1 * z * z % q)], [str(y0 * z ** 3 % q), str(y1 * z ** 3 % q)], [str(z), "0"]]
+
+    d = {"vk_alfa_1": g1(), "vk_beta_1": g1(), "vk_beta_2": g2(), "vk_delta_1": g1(), "vk_delta_2": g2()}
+    nA = num()
+    d["A"] = [g1() for _ in range(nA)]
+    ds, nidx = num(), num()
+    idx = [num() for _ in range(nidx)]
+    assert num() == nidx
+    B1 = [["0", "1", "0"]] * ds; B2 = [[["0", "0"], ["1", "0"], ["0", "0"]]] * ds
+    B1, B2 = list(B1), list(B2)
+    for i in idx:
+        B2[i] = g2(); B1[i] = g1()
+    d["B1"], d["B2"] = B1, B2
+    d["hExps"] = [g1() for _ in range(num())]
+    d["C"] = [["0", "1", "0"], ["0", "1", "0"]] + [g1() for _ in range(num())]
+    assert pos[0] == len(full)
+    assert H.pk_bellman2ethsnarks(json.dumps(d)) == k.serialize(orc.FMT_ALT_NOZK)
+    assert H.pk_bellman2ethsnarks(d, alt=False) == k.serialize(orc.FMT_MCL_NOZK)
