@@ -10,6 +10,7 @@
 #include <thread>
 #include <mutex>
 #include <condition_variable>
+#include <nvtx3/nvToolsExt.h>      // header-only; the ranges are no-ops unless a profiler injects itself
 
 using namespace b200;
 
@@ -87,6 +88,7 @@ void b200_ctx::t_begin(const char* name) {
     cudaEventCreate(&a); cudaEventCreate(&b);
     cudaEventRecord(a, cur());
     timing_events.push_back({name, {a, b}});
+    nvtx_ids.push_back((unsigned long long)nvtxRangeStartA(name));
 }
 void b200_ctx::t_end() {
     if (!timing_enabled) return;
@@ -94,6 +96,7 @@ void b200_ctx::t_end() {
     for (size_t i = timing_events.size(); i-- > 0;) {
         if (timing_events[i].first.empty() || timing_events[i].first[0] != '#') {
             cudaEventRecord(timing_events[i].second.second, cur());
+            if (i < nvtx_ids.size()) nvtxRangeEnd((nvtxRangeId_t)nvtx_ids[i]);
             timing_events[i].first = "#" + timing_events[i].first;
             return;
         }
@@ -111,6 +114,7 @@ void b200_ctx::t_collect() {
     }
     for (auto& ev : timing_events) { cudaEventDestroy(ev.second.first); cudaEventDestroy(ev.second.second); }
     timing_events.clear();
+    nvtx_ids.clear();
 }
 
 namespace {
@@ -331,7 +335,6 @@ int b200_set_option(b200_ctx* ctx, const char* name, long value) {
     else if (!strcmp(name, "finalize_chunks")) ctx->finalize_chunks = (int)value;
     else if (!strcmp(name, "finalize_big_seg")) ctx->finalize_big_seg = (int)value;
     else if (!strcmp(name, "split_chains")) ctx->split_chains = (int)value;
-    else if (!strcmp(name, "affine_rounds")) ctx->affine_rounds = (int)value;
     else return B200_ERR_ARG;
     return B200_OK;
 }

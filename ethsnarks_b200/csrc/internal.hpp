@@ -21,12 +21,11 @@ struct b200_ctx {
     std::vector<std::pair<std::string, std::pair<cudaEvent_t, cudaEvent_t>>> timing_events;
     std::vector<std::pair<std::string, float>> timings;
     std::vector<float> timing_starts;   // start of each phase relative to the first phase of the call, ms
+    std::vector<unsigned long long> nvtx_ids;   // NVTX range of each phase (same names; no-ops unless a tool is attached)
     bool timing_enabled = true;
     unsigned long long launches = 0;   // kernels launched by this library since init
     int window_override = 0;           // 0 = cost model
     int chunk_override = 0;            // 0 = auto
-    int affine_rounds = 0;             // batched-affine pre-reduction rounds before the XYZZ accumulate (experimental:
-                                       // correct but slower than XYZZ alone on B200); -1 = by run length
     int g2_acc_smem = 0;               // dynamic shared memory requested by msm_accumulate<G2> only to cap its blocks per SM,
                                        // so that G1 accumulate blocks of the other lanes are co-resident with it
     int g2_pair = 2;                   // G2 accumulate with one point per lane pair (msm_acc_pair.cuh): 2 = lazy operand forms,

@@ -44,9 +44,9 @@ void launch_accumulate(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const u
     typedef typename G::Pt Pt;
     if constexpr (sizeof(Pt) > 128) {
         if (ctx->g2_pair) {     // one point per lane pair (msm_acc_pair.cuh)
-            const unsigned grid = (unsigned)((2 * p.nchunks + 127) / 128);
+            const unsigned grid = (unsigned)((2 * p.nchunks + B200_G2_PAIR_BLOCK - 1) / B200_G2_PAIR_BLOCK);
 #define B200_PAIR_LAUNCH(MODE)                                                                                              \
-    msm_accumulate_g2_pair<G, MODE><<<grid, 128, 0, st>>>(skeys, svals, offsets, p.nb, p.L, (const G2Affine*)d_bases, (G2XYZZ*)buckets, \
+    msm_accumulate_g2_pair<G, MODE><<<grid, B200_G2_PAIR_BLOCK, 0, st>>>(skeys, svals, offsets, p.nb, p.L, (const G2Affine*)d_bases, (G2XYZZ*)buckets, \
                                                           (G2XYZZ*)pfirst, (G2XYZZ*)plast)
             if (ctx->g2_pair == 1) B200_PAIR_LAUNCH(1);          // strict operand preparation, kept as cross-check
             else if (ctx->g2_pair == 3) B200_PAIR_LAUNCH(3);     // lazy operands + out-of-line products

@@ -165,8 +165,16 @@ static B200_DEV void pair_store(G2XYZZ* dst, bool imag, const HalfXYZZ& a) {
 #ifndef B200_G2_PAIR_MINB
 #define B200_G2_PAIR_MINB 3     // 168 registers, no spills (4 -> 128 registers with spills: 7.8 ms against 7.5 ms)
 #endif
+#ifndef B200_G2_PAIR_BLOCK
+#define B200_G2_PAIR_BLOCK 128  // threads per block (registers are allocated per warp: smaller blocks give finer occupancy steps)
+#endif
+#ifdef B200_G2_PAIR_MAXREG        // experiment knob: an explicit register cap instead of the launch bounds
+#define B200_G2_PAIR_BOUNDS __maxnreg__(B200_G2_PAIR_MAXREG)
+#else
+#define B200_G2_PAIR_BOUNDS __launch_bounds__(B200_G2_PAIR_BLOCK, B200_G2_PAIR_MINB)
+#endif
 template <typename G, int MODE>   // G2T only; a template so that only the G2 translation unit emits it
-__global__ void __launch_bounds__(128, B200_G2_PAIR_MINB) msm_accumulate_g2_pair(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+__global__ void B200_G2_PAIR_BOUNDS msm_accumulate_g2_pair(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
                                                                              const uint64_t* __restrict__ offsets, uint32_t nb, uint32_t L,
                                                                              const G2Affine* __restrict__ bases, G2XYZZ* __restrict__ buckets,
                                                                              G2XYZZ* __restrict__ pfirst, G2XYZZ* __restrict__ plast) {

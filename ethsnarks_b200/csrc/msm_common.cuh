@@ -69,10 +69,6 @@ template <typename G>
 void launch_accumulate(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* skeys, const uint32_t* svals,
                        const uint64_t* offsets, const void* d_bases, void* buckets, void* pfirst, void* plast);
 template <typename G>
-void launch_affine_rounds(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, int n_rounds, const uint32_t* skeys, const uint32_t* svals,
-                          const void* d_bases, const uint64_t* offsets, const uint32_t** keys_out, const void** pts_out,
-                          const uint64_t** off_out);
-template <typename G>
 void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uint32_t* keys, const uint64_t* offsets, void* buckets,
                      const void* pfirst, const void* plast, uint32_t* big, size_t big_cap);
 template <typename G>

@@ -188,24 +188,7 @@ static void msm_run_t(b200_ctx* ctx, const void* d_bases, const void* d_scalars,
     if (table_c && (uint64_t)table_stride * ((255 + table_c - 1) / table_c) >= (1ull << 31)) throw std::runtime_error("msm: table too large for 31-bit point indices");
     MsmPlan p = make_plan(ctx, n, table_c, sizeof(Pt) > 128 && ctx->g2_pair != 0);
     const MsmSorted so = msm_sort_stage(ctx, st, p, d_scalars, d_gather, n, scalars_mont, table_stride, false);
-    // batched-affine pre-reduction: R rounds leave runs 2^R times shorter for the XYZZ accumulate
-    int rounds = ctx->affine_rounds;
-    if (rounds < 0) {
-        const double avg_run = (double)p.pairs / (double)p.nb;
-        rounds = 0;
-        while (rounds < 4 && avg_run >= (double)(8 << rounds)) ++rounds;      // keep >= ~4 per run for the accumulate
-    }
-    const uint32_t* akeys = so.keys;
-    const uint32_t* avals = so.vals;
-    const void* abases = d_bases;
-    const uint64_t* aoff = so.offsets;
-    if (rounds > 0) {
-        ctx->t_begin("msm.affine");
-        launch_affine_rounds<G>(ctx, st, p, rounds, so.keys, so.vals, d_bases, so.offsets, &akeys, &abases, &aoff);
-        avals = nullptr;
-        ctx->t_end();
-    }
-    msm_tail<G>(ctx, st, p, akeys, avals, aoff, abases, d_out);
+    msm_tail<G>(ctx, st, p, so.keys, so.vals, so.offsets, d_bases, d_out);
 }
 
 // One MSM of a shared list (internal.hpp: MsmShared) against this group's window table (W * stride entries + the zero entry).

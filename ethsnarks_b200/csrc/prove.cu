@@ -991,7 +991,7 @@ void run_msms_witness_only(b200_key* k, const Acc& a, bool want_b1, int finish =
         v1 = std::max<uint64_t>(std::max<uint64_t>(k->A_first + k->nA, k->B_first + k->nB), l0 + k->nL);
     }
     const uint64_t nvar = v1 - v0;
-    const bool share = ctx->shared_sort && ctx->affine_rounds == 0 && (k->world == 1 || (k->A_ident && k->B_ident)) && k->A_t && k->B2_t && k->L_t &&
+    const bool share = ctx->shared_sort && (k->world == 1 || (k->A_ident && k->B_ident)) && k->A_t && k->B2_t && k->L_t &&
                        k->A_pos && k->B_pos && k->cA == k->cB && k->cA == k->cL && k->cA >= 8 /* <= 32 windows */ && (!want_b1 || k->B1_t) &&
                        k->nv + 1 < (1ull << B200_SHARED_VAR_BITS) && 5 * k->nA >= 4 * nvar && 5 * k->nB >= 4 * nvar && 5 * k->nL >= 4 * nvar;
     if (share) {

@@ -87,7 +87,7 @@ unsigned long long b200_launch_count(b200_ctx* ctx);     /* kernels launched by 
  *   "reduce_1d"       1 = running-sum bucket reduction instead of the two-dimensional one
  *   "ntt_radix4"      1 = NTT passes with two stages per shared-memory round trip (default), 0 = one
  *   "shared_sort"     1 = the witness MSMs of one prove consume ONE sorted digit list when their queries are dense (default)
- *   "affine_rounds"   batched-affine pre-reduction rounds before the accumulate (0 = off, default; -1 = by run length) */
+ */
 int b200_set_option(b200_ctx* ctx, const char* name, long value);
 int b200_timing_count(b200_ctx* ctx);                    /* phase timings (CUDA events) of the last call */
 int b200_timing_get(b200_ctx* ctx, int i, char* name, size_t cap, float* ms);

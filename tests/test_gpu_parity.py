@@ -223,36 +223,6 @@ def test_msm_window_override(ctx, window):
         assert ginf == winf and np.array_equal(got, want), reduce_1d
 
 
-@pytest.mark.parametrize("group", [1, 2])
-def test_msm_batched_affine_rounds(ctx, group):
-    """The optional batched-affine pre-reduction rounds (msm_aff.cuh) give the same sums: dense scalars, duplicate bases
-    (tangent case), P + (-P), infinity bases, with and without window tables."""
-    n = 3000
-    k = orc.sha512_rng_fr(1 << 45, n)
-    fix, omsm = (orc.g1_fixed_base, orc.msm_g1) if group == 1 else (orc.g2_fixed_base, orc.msm_g2)
-    xy, inf = fix(k)
-    inf[7] = 1
-    xy[21] = xy[20]; xy[23] = xy[22]
-    s = _scalar_mix(n, 33, "dense")
-    s[21] = s[20]                                                   # same point, same digits: doubling inside a bucket
-    s[23] = orc.fr_sub(np.zeros((1, 4), np.uint64), s[22:23])[0]    # P and -P cancel
-    want, winf = omsm(xy, inf, s)
-    plain, tabled = eb.Bases(ctx, group, xy=xy, inf=inf), eb.Bases(ctx, group, xy=xy, inf=inf)
-    try:
-        for window, rounds in ((0, 2), (6, 4), (9, -1)):
-            ctx.set_option("affine_rounds", rounds)
-            ctx.set_option("window", window)
-            got, gi = plain.msm(s)
-            assert gi == winf and np.array_equal(got, want), (window, rounds, "plain")
-            tabled.precompute(window)
-            got, gi = tabled.msm(s)
-            assert gi == winf and np.array_equal(got, want), (window, rounds, "tables")
-    finally:
-        ctx.set_option("affine_rounds", 0)
-        ctx.set_option("window", 0)
-        plain.free(); tabled.free()
-
-
 def test_msm_g2_two_dimensional_reduction(ctx):
     n = 3000
     bases, inf = orc.g2_fixed_base(orc.sha512_rng_fr(1 << 44, n))

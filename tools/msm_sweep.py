@@ -42,7 +42,6 @@ def main():
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--table-window", type=int, default=0, help="window size c of the fixed-base tables (0 = cost model)")
     ap.add_argument("--groups", default="1,2")
-    ap.add_argument("--affine-rounds", type=int, default=0)
     ap.add_argument("--opt", action="append", default=[], help="library option name=value, repeatable")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -56,7 +55,6 @@ def main():
     peak = ctx.imad_peak(5)
     if args.chunk:
         ctx.set_option("chunk", args.chunk)
-    ctx.set_option("affine_rounds", args.affine_rounds)
     for kv in args.opt:
         name, _, val = kv.partition("=")
         ctx.set_option(name, int(val))
@@ -141,7 +139,7 @@ def main():
                               "imad_peak_tmac_s": peak / 1e12, "in_exponent_ok": ok, "tables": bool(args.tables), "mix": args.mix, "ms_min": float(np.min(times)),
                               "reps": len(times), "precompute_ms": pre_ms, "window": int(ctx.last_window()) if hasattr(ctx, "last_window") else None,
                               "cpu_reference": cpu, "speedup_vs_cpu": (cpu["ms"] / ms) if cpu else None,
-                              "chunk": args.chunk, "affine_rounds": args.affine_rounds,
+                              "chunk": args.chunk,
                               "phases_ms": {kk: round(float(np.median(v)), 4) for kk, v in sub.items()}}), flush=True)
             bases.free()
             del s_dev
