@@ -578,7 +578,7 @@ def main():
     ap.add_argument("--log-m", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="both", choices=["both", "shard", "replicas"])
-    ap.add_argument("--cpu-budget-s", type=float, default=200.0, help="--impl reference: bound on the summed prover time")
+    ap.add_argument("--cpu-budget-s", type=float, default=120.0, help="--impl reference: bound on the summed prover time")
     ap.add_argument("--ref-phases", action="store_true", help="--impl reference: also report the reference's own block timers")
     ap.add_argument("--flavour", default="field", choices=["field", "binary"],
                     help="R1CS generator: r1cs_examples.tcc:25-93 (uniform field witness) or :100-157 (0/1 witness)")
