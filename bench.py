@@ -75,6 +75,7 @@ class ShardedProver:
         self.key, self.world, self.rank, self.stream = key, world, rank, stream
         self.part = torch.zeros(32, dtype=torch.int64, device=dev)             # 256 B: A 64 | B 128 | C 64
         self.parts = torch.zeros(32 * world, dtype=torch.int64, device=dev)
+        self.w_stage = None
         # staged form: the ranks also share the transform work - each of the three evaluation vectors goes through the witness
         # map and its first two transforms on ONE rank and is broadcast (NCCL, on the library's stream) to the others
         self.staged = staged and world > 1
@@ -84,7 +85,19 @@ class ShardedProver:
             ptrs, nbytes = key.buffers()
             self.vecs = [torch.as_tensor(DeviceBuffer(p, nbytes), device=dev) for p in ptrs]
 
-    def __call__(self, wptr):
+    def __call__(self, wptr, host=None):
+        if host is not None and self.world > 1:
+            # the witness starts in (pinned) host memory: rank 0 uploads it ONCE and it is broadcast over NVLink, instead of
+            # every rank pulling its own copy through the host's memory system at the same time (ncclBroadcast of w)
+            import torch
+            import torch.distributed as dist
+            if self.w_stage is None or self.w_stage.shape != host.shape:
+                self.w_stage = torch.empty(host.shape, dtype=host.dtype, device=self.part.device)
+            with torch.cuda.stream(self.stream):
+                if self.rank == 0:
+                    self.w_stage.copy_(host, non_blocking=True)
+                dist.broadcast(self.w_stage, src=0)
+            wptr = self.w_stage.data_ptr()
         if self.staged:
             import torch
             import torch.distributed as dist
@@ -387,14 +400,16 @@ def run_ours(args):
 
     sharded_prove = ShardedProver(key, world, rank, stream, dev, staged=bool(args.staged)) if shard else None
 
-    def step(wptr):
-        return sharded_prove(wptr) if shard else key.prove(wptr)
+    def step(wptr, host=None):
+        """wptr: device or host pointer of the witness; host: the pinned host tensor when the witness starts on the host"""
+        return sharded_prove(wptr, host) if shard else key.prove(wptr)
 
     def timed(bufs, steps, collect):
         it = [0]
 
         def one():
-            step(bufs[it[0] % len(bufs)].data_ptr())
+            b = bufs[it[0] % len(bufs)]
+            step(b.data_ptr(), None if b.is_cuda else b)
             it[0] += 1
         return timed_steps(one, steps, collect)
 
@@ -457,7 +472,7 @@ def run_ours(args):
         ms_e2e, _ = timed_pipelined([w_pin.data_ptr(), w2_pin.data_ptr()], args.steps)
     else:
         for wp in w_pins:
-            step(wp.data_ptr())
+            step(wp.data_ptr(), wp)
         ms_e2e, _ = timed(w_pins, args.steps, None)
     # per-kernel durations for the roofline: the same steps with the MSM lanes serialised, so that each kernel's
     # CUDA-event bracket on its launching stream contains that kernel alone

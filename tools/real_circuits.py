@@ -42,6 +42,7 @@ def main():
             pk.prove(w)
             wall.append((time.perf_counter() - t0) * 1e3)
             dev.append(dict(ctx.timings())["prove.total"])
+        timeline = [(n, round(a, 3), round(d, 3)) for n, a, d in ctx.timeline()]
         ones = int(np.sum(np.all(w == np.asarray(orc.constants()[8:12], np.uint64), axis=1)))
         zeros = int(np.sum(~w.any(axis=1)))
         cpu = orc_ref.prove(circ, w, key, repeats=4, threads=os.cpu_count(), all_times=True)[2][1:]
@@ -49,7 +50,7 @@ def main():
                           "witness_zero_or_one": (zeros + ones) / float(circ.nv + 1),
                           "gpu_prove_wall_ms_median": float(np.median(wall)), "gpu_prove_device_ms_median": float(np.median(dev)),
                           "reference_cpu_prove_ms_median": float(np.median(cpu)) * 1e3, "cpu_threads": os.cpu_count(),
-                          "speedup": float(np.median(cpu)) * 1e3 / float(np.median(wall)), "proof_equals_golden": True}), flush=True)
+                          "speedup": float(np.median(cpu)) * 1e3 / float(np.median(wall)), "proof_equals_golden": True, "timeline_name_start_ms_dur_ms": timeline}), flush=True)
         pk.free()
 
 
