@@ -54,7 +54,7 @@ template <> struct Gen<Fq2> {
     }
 };
 
-#define B200_BIG_SPAN 64    // a bucket spanning more chunks than this goes to the block-per-bucket reduction
+#define B200_BIG_SPAN 8     // a bucket spanning more chunks than this goes to the block-per-bucket reduction (one thread chains the additions below it: 64 cost 0.5 ms per G2 bucket on small real circuits)
 struct MsmPlan {
     int c, W, keybits, table;
     uint32_t half, nb, L, S, nseg;

@@ -134,6 +134,72 @@ __global__ void __launch_bounds__(128) msm_finalize_big(const uint64_t* __restri
     }
 }
 
+// The giant-bucket sums for G2 with one point per LANE PAIR: 64 pairs per 128-thread block, tree through shared memory.  A one-
+// thread G2 addition is ~20 us of dependent work, the lane-pair form about half; on small real circuits this finalize is the
+// longest link of the B(G2) lane (EdDSA: 0.66 of 1.42 ms).  Same inputs and outputs as msm_finalize_big_seg / msm_finalize_big.
+template <int MODE>
+B200_DEV void block_tree_reduce_pair(const PairLane<MODE>& ln, HalfXYZZ& acc, G2XYZZ* sh) {     // blockDim.x == 128: 64 pairs; result in pair 0
+    const uint32_t pair = threadIdx.x >> 1;
+    pair_store(&sh[pair], ln.imag, acc);
+    __syncthreads();
+    for (uint32_t stride = 32; stride > 0; stride >>= 1) {
+        if (pair < stride) {
+            pair_add_full(ln, acc, pair_load(&sh[pair + stride], ln.imag));
+            pair_store(&sh[pair], ln.imag, acc);
+        }
+        __syncthreads();
+    }
+}
+template <typename G>
+__global__ void __launch_bounds__(128) msm_finalize_big_seg_pair(const uint64_t* __restrict__ offsets, uint32_t L, const G2XYZZ* __restrict__ pfirst,
+                                                                 const uint32_t* __restrict__ big_count, const uint32_t* __restrict__ big_list,
+                                                                 G2XYZZ* __restrict__ segp) {
+    __shared__ G2XYZZ sh[64];
+    PairLane<2> ln;
+    ln.imag = threadIdx.x & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    const uint32_t pair = threadIdx.x >> 1;
+    const uint32_t nbig = min(*big_count, (uint32_t)B200_BIG_FAST);
+    for (uint32_t j = blockIdx.y; j < nbig; j += gridDim.y) {
+        const uint32_t b = big_list[j];
+        const uint64_t t0 = offsets[b] / L, t1 = (offsets[b + 1] - 1) / L;
+        const uint64_t per = (t1 - t0 + B200_BIG_SEGS - 1) / B200_BIG_SEGS;
+        const uint64_t lo = t0 + 1 + (uint64_t)blockIdx.x * per, hi = min(lo + per, t1 + 1);
+        HalfXYZZ acc = ln.inf();
+        for (uint64_t t = lo + pair; t < hi; t += 64) pair_add_full(ln, acc, pair_load(&pfirst[t], ln.imag));
+        block_tree_reduce_pair(ln, acc, sh);
+        if (pair == 0) pair_store(&segp[(size_t)j * B200_BIG_SEGS + blockIdx.x], ln.imag, acc);
+        __syncthreads();
+    }
+}
+template <typename G>
+__global__ void __launch_bounds__(128) msm_finalize_big_pair(const uint64_t* __restrict__ offsets, uint32_t L, G2XYZZ* __restrict__ buckets,
+                                                             const G2XYZZ* __restrict__ pfirst, const G2XYZZ* __restrict__ plast,
+                                                             const uint32_t* __restrict__ big_count, const uint32_t* __restrict__ big_list,
+                                                             const G2XYZZ* __restrict__ segp) {
+    __shared__ G2XYZZ sh[64];
+    PairLane<2> ln;
+    ln.imag = threadIdx.x & 1;
+    ln.mask = 3u << (threadIdx.x & 30);
+    const uint32_t pair = threadIdx.x >> 1;
+    const uint32_t nbig = *big_count;
+    for (uint32_t j = blockIdx.x; j < nbig; j += gridDim.x) {
+        const uint32_t b = big_list[j];
+        const uint64_t s = offsets[b], e = offsets[b + 1];
+        const uint64_t t0 = s / L, t1 = (e - 1) / L;
+        HalfXYZZ acc = ln.inf();
+        if (pair == 0) acc = pair_load((s == t0 * L) ? &pfirst[t0] : &plast[t0], ln.imag);
+        if (segp && j < B200_BIG_FAST) {
+            for (uint32_t x = pair; x < B200_BIG_SEGS; x += 64) pair_add_full(ln, acc, pair_load(&segp[(size_t)j * B200_BIG_SEGS + x], ln.imag));
+        } else {
+            for (uint64_t t = t0 + 1 + pair; t <= t1; t += 64) pair_add_full(ln, acc, pair_load(&pfirst[t], ln.imag));
+        }
+        block_tree_reduce_pair(ln, acc, sh);
+        if (pair == 0) pair_store(&buckets[b], ln.imag, acc);
+        __syncthreads();
+    }
+}
+
 // ------------------------------------------------------------------------------------------------- 6. reductions
 // one thread per segment of S consecutive buckets of one window: sum_{b in seg} (b+1) * B_b
 template <typename G>
@@ -512,12 +578,21 @@ void launch_finalize(b200_ctx* ctx, cudaStream_t st, const MsmPlan& p, const uin
         msm_finalize<G><<<(p.nb + 127) / 128, 128, 0, st>>>(offsets, p.nb, p.L, buckets, pfirst, plast, big, big + 1);
     }
     Pt* segp = nullptr;
+    bool pair_big = false;
+    if constexpr (sizeof(Pt) > 128) pair_big = ctx->pair_reduce != 0 && ctx->pair_tail != 0;
     if (ctx->finalize_big_seg) {
         segp = (Pt*)ctx->scratch("msm_big_seg", (size_t)B200_BIG_FAST * B200_BIG_SEGS * sizeof(Pt));
-        msm_finalize_big_seg<G><<<dim3(B200_BIG_SEGS, 8), 128, smem, st>>>(offsets, p.L, pfirst, big, big + 1, segp);
+        if constexpr (sizeof(Pt) > 128) {
+            if (pair_big) msm_finalize_big_seg_pair<G><<<dim3(B200_BIG_SEGS, 8), 128, 0, st>>>(offsets, p.L, (const G2XYZZ*)pfirst, big, big + 1, (G2XYZZ*)segp);
+        }
+        if (!pair_big) msm_finalize_big_seg<G><<<dim3(B200_BIG_SEGS, 8), 128, smem, st>>>(offsets, p.L, pfirst, big, big + 1, segp);
         ctx->launches++;
     }
-    msm_finalize_big<G><<<(unsigned)std::min<size_t>(big_cap, 1024), 128, smem, st>>>(offsets, p.L, buckets, pfirst, plast, big, big + 1, segp);
+    if constexpr (sizeof(Pt) > 128) {
+        if (pair_big) msm_finalize_big_pair<G><<<(unsigned)std::min<size_t>(big_cap, 1024), 128, 0, st>>>(
+                          offsets, p.L, (G2XYZZ*)buckets, (const G2XYZZ*)pfirst, (const G2XYZZ*)plast, big, big + 1, (const G2XYZZ*)segp);
+    }
+    if (!pair_big) msm_finalize_big<G><<<(unsigned)std::min<size_t>(big_cap, 1024), 128, smem, st>>>(offsets, p.L, buckets, pfirst, plast, big, big + 1, segp);
     ctx->launches += 2;
 }
 
