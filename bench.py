@@ -32,12 +32,29 @@ sys.path.insert(0, ROOT)
 
 MAC_PER_G1_POINT = 23936     # 16 windows x 11 modmul x 136 MAC
 MAC_PER_G2_POINT = 63104     # 16 x 29 x 136
+# what the kernels execute per mixed addition: G1 8 products x 136 + one two-product row set (Y3) x 200;
+# G2 per lane of the pair 6 x 200 + 2 squarings x 136 + one four-product row set x 328, two lanes
+MAC_PER_G1_ADD = 8 * 136 + 200
+MAC_PER_G2_ADD = 2 * (6 * 200 + 2 * 136 + 328)
 BYTES_PER_G1_POINT = 96      # 64 B affine base + 32 B scalar
 BYTES_PER_G2_POINT = 160
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the accumulate kernel at 2^20 points, from the ncu --set full
 # capture summarised in profiles/r1_ncu_msm_accumulate_2p20_full.csv (window tables: 13 table points are read per scalar,
 # so the traffic is ~12x the canonical 96/160 B per point; HBM stays under 11 % busy)
 NCU_TRAFFIC_BYTES = {("G2", 20): 1.880513e9 + 0.169542e9, ("G1", 20): 1.854417e9 + 0.102273e9}   # profiles/r1_ncu_msm_accumulate_2p20_v2.csv
+
+
+def table_windows(n, override=0):
+    """Windows per scalar of a fixed-base-table MSM over n bases: the cost model of choose_window(n, true)
+    (ethsnarks_b200/csrc/msm_impl.cuh), restated here only to annotate the roofline with the executed multiply-adds."""
+    best_c, best = 8, float("inf")
+    for c in range(6, 23):
+        W = (255 + c - 1) // c
+        cost = n * W * 11.5 + (2.0 ** (c - 1)) * 34.0
+        if cost < best:
+            best, best_c = cost, c
+    c = max(4, min(24, override)) if override else best_c
+    return (255 + c - 1) // c
 
 
 # ----------------------------------------------------------------------------------------------- multi-rank helpers
@@ -524,6 +541,7 @@ def run_ours(args):
                 agg.setdefault(name, []).append(ms)
     mean = {k: float(np.mean(v)) for k, v in agg.items()}
     msm_names = ["A", "B_g2", "H", "L"]
+    tables_on = not any(kv.split("=")[0] == "tables" and int(kv.split("=")[1]) == 0 for kv in args.opt)
     counts = {"A": key.info()["nA"], "B_g2": key.info()["nB"], "H": key.info()["nH"], "L": key.info()["nL"]}
     kernels = {}
     for nm in msm_names:
@@ -535,6 +553,13 @@ def run_ours(args):
             kernels[nm] = {"kernel": "msm_accumulate_g2_pair" if g2 else "msm_accumulate<G1>", "points": counts[nm], "ms": ms,
                            "tmac_s": mac / (ms * 1e-3) / 1e12, "frac_imad": mac / (ms * 1e-3) / imad_peak,
                            "gb_s": byts / (ms * 1e-3) / 1e9}
+            if tables_on and counts[nm]:
+                # upper bound on the multiply-adds the kernel executes: one mixed addition per (scalar, window) pair; the
+                # first point of a bucket run is a copy and zero digits are skipped, so the true count is a little lower
+                W = table_windows(counts[nm], args.window)
+                mac_x = (MAC_PER_G2_ADD if g2 else MAC_PER_G1_ADD) * W * counts[nm]
+                kernels[nm]["executed"] = {"windows": W, "mac_per_point": mac_x // counts[nm], "tmac_s": mac_x / (ms * 1e-3) / 1e12,
+                                           "frac_imad": mac_x / (ms * 1e-3) / imad_peak}
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -547,6 +572,9 @@ def run_ours(args):
         kd = kernels[dom]
         roofline = {"bound": "imad", "kernel": kd["kernel"] + " (%s query)" % dom, "achieved": kd["tmac_s"], "peak": imad_peak / 1e12,
                     "unit": "TMAC/s", "frac": kd["frac_imad"],
+                    "note": "achieved/frac use SURVEY.md §8(d)'s canonical count (16 windows x 11 / 29 products x 136); the kernels run "
+                            "fewer windows (fixed-base tables) and cheaper additions, so frac can exceed 1 - `executed` counts what they run",
+                    "executed": kd.get("executed"),
                     "traffic": NCU_TRAFFIC_BYTES.get(("G2" if dom == "B_g2" else "G1", args.log_m)) if world == 1 or not shard else None,
                     "peak_source": "b200_imad_peak microbenchmark (IMAD.WIDE.U32, all SMs), measured in this run",
                     "hbm": {"achieved": kd["gb_s"], "peak": hbm_peak, "unit": "GB/s", "frac": kd["gb_s"] / hbm_peak,

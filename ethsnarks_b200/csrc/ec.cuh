@@ -76,7 +76,7 @@ struct XYZZ {
         }
         F PP = Pp.sqr(), PPP = Pp * PP, Q = X * PP;
         F X3 = R.sqr() - PPP - Q.dbl();
-        Y = R * (Q - X3) - Y * PPP;
+        Y = diff_of_products(R, Q - X3, Y, PPP);
         X = X3;
         ZZ = ZZ * PP; ZZZ = ZZZ * PPP;
     }
@@ -92,7 +92,7 @@ struct XYZZ {
         }
         F PP = Pp.sqr(), PPP = Pp * PP, Q = U1 * PP;
         F X3 = R.sqr() - PPP - Q.dbl();
-        Y = R * (Q - X3) - S1 * PPP;
+        Y = diff_of_products(R, Q - X3, S1, PPP);
         X = X3;
         ZZ = ZZ * o.ZZ * PP; ZZZ = ZZZ * o.ZZZ * PPP;
     }

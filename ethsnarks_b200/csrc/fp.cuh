@@ -388,6 +388,46 @@ struct __align__(16) Fp {
         }
         return mont_final(E, O);
     }
+    // (a0*b0 + a1*b1 + a2*b2 + a3*b3) * R^-1 mod p, fully reduced, with ONE reduction (328 multiply-adds against 400 for two
+    // dot2): the imaginary/real component of x*y - z*w in Fq2 as seen by one lane of the lane-pair G2 kernel.  Operands
+    // at most p (canonical values or neg_lazy of them).  Bound: a row adds at most 4 p 2^32 + p 2^32 to a running total that
+    // the previous shift left below p(5 + 2^-29), so every total stays below 5p(2^32 + 1.1) < 0.946 * 2^288 (p < 0.18904 * 2^256):
+    // the odd-aligned accumulator never carries out; the result is below p(4p/R + 1) < 1.76p, one conditional subtraction.
+    static B200_DEV Fp dot4(const Fp& a0, const Fp& b0, const Fp& a1, const Fp& b1, const Fp& a2, const Fp& b2, const Fp& a3, const Fp& b3) {
+        uint32_t E[8], O[8];
+        _Pragma("unroll") for (int j = 0; j < 8; j += 2) {
+            uint64_t te = (uint64_t)a0.v[j] * b0.v[0], to = (uint64_t)a0.v[j + 1] * b0.v[0];
+            E[j] = (uint32_t)te; E[j + 1] = (uint32_t)(te >> 32);
+            O[j] = (uint32_t)to; O[j + 1] = (uint32_t)(to >> 32);
+        }
+        chain_mad(O, a1.v[1], a1.v[3], a1.v[5], a1.v[7], b1.v[0]);
+        chain_mad_carry(E, O[7], a1.v[0], a1.v[2], a1.v[4], a1.v[6], b1.v[0]);
+        chain_mad(O, a2.v[1], a2.v[3], a2.v[5], a2.v[7], b2.v[0]);
+        chain_mad_carry(E, O[7], a2.v[0], a2.v[2], a2.v[4], a2.v[6], b2.v[0]);
+        chain_mad(O, a3.v[1], a3.v[3], a3.v[5], a3.v[7], b3.v[0]);
+        chain_mad_carry(E, O[7], a3.v[0], a3.v[2], a3.v[4], a3.v[6], b3.v[0]);
+        {
+            uint32_t m = E[0] * P::INV;
+            chain_mad(O, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+            chain_mad_carry(E, O[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+        }
+        _Pragma("unroll") for (int i = 1; i < 8; ++i) {
+            uint32_t* X = (i & 1) ? O : E;
+            uint32_t* Y = (i & 1) ? E : O;
+            chain_shift_mad(Y, X[0], a0.v[1], a0.v[3], a0.v[5], a0.v[7], b0.v[i]);
+            chain_mad_carry(X, Y[7], a0.v[0], a0.v[2], a0.v[4], a0.v[6], b0.v[i]);
+            chain_mad(Y, a1.v[1], a1.v[3], a1.v[5], a1.v[7], b1.v[i]);
+            chain_mad_carry(X, Y[7], a1.v[0], a1.v[2], a1.v[4], a1.v[6], b1.v[i]);
+            chain_mad(Y, a2.v[1], a2.v[3], a2.v[5], a2.v[7], b2.v[i]);
+            chain_mad_carry(X, Y[7], a2.v[0], a2.v[2], a2.v[4], a2.v[6], b2.v[i]);
+            chain_mad(Y, a3.v[1], a3.v[3], a3.v[5], a3.v[7], b3.v[i]);
+            chain_mad_carry(X, Y[7], a3.v[0], a3.v[2], a3.v[4], a3.v[6], b3.v[i]);
+            uint32_t m = X[0] * P::INV;
+            chain_mad(Y, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+            chain_mad_carry(X, Y[7], P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+        }
+        return mont_final(E, O);
+    }
 #ifndef B200_FP_SQR_DEDICATED
 #define B200_FP_SQR_DEDICATED 0     // measured on B200 (round 2): correct (all GPU parity tests green with 1) but NOT faster - see below
 #endif
@@ -572,5 +612,20 @@ struct Fq2 {
         return Fq2{a * n, (b * n).neg()};
     }
 };
+
+// x*y - z*w, the Y coordinate of every XYZZ addition (R (Q - X3) - Y1 PPP).  In the prime field it is one two-product row
+// set under ONE reduction (Fp::dot2 with z entering as p - z: 200 multiply-adds against 272 and a modular subtraction).
+#ifndef B200_FUSED_Y
+#define B200_FUSED_Y 1
+#endif
+template <typename P>
+B200_DEV Fp<P> diff_of_products(const Fp<P>& x, const Fp<P>& y, const Fp<P>& z, const Fp<P>& w) {
+#if B200_FUSED_Y
+    return Fp<P>::dot2(x, y, z.neg_lazy(), w);
+#else
+    return x * y - z * w;
+#endif
+}
+B200_DEV Fq2 diff_of_products(const Fq2& x, const Fq2& y, const Fq2& z, const Fq2& w) { return x * y - z * w; }
 
 }  // namespace b200

@@ -14,6 +14,10 @@
 
 namespace b200 {
 
+#ifndef B200_PAIR_FUSED_Y
+#define B200_PAIR_FUSED_Y 1     // R (Q - X3) - Y PPP as one four-product row set (PairLane::diff)
+#endif
+
 struct HalfXYZZ { Fq X, Y, ZZ, ZZZ; };   // one Fq2 component of a G2 XYZZ point
 
 // (fp.cuh: neg_lazy, add_lazy, sub_lazy; the products themselves still return fully reduced values, so everything
@@ -54,6 +58,17 @@ struct PairLane {
         const Fq t = sel(imag, LAZY ? Fq::add_lazy(xo, xo) : xo.dbl(), LAZY ? Fq::sub_lazy(xm, xo) : xm - xo);
         if (OOL) return pair_mul_ool(s, t);
         return s * t;
+    }
+    // my component of x * y - z * w under ONE reduction (Fq::dot4: 328 multiply-adds against 400 for two products)
+    B200_DEV Fq diff(const Fq& xm, const Fq& xo, const Fq& ym, const Fq& yo, const Fq& zm, const Fq& zo, const Fq& wm, const Fq& wo) const {
+#if B200_PAIR_FUSED_Y
+        const Fq nzm = zm.neg_lazy(), nzo = zo.neg_lazy();
+        const Fq p = sel(imag, xo, xm), q = sel(imag, xm, xo.neg_lazy());          // real: xa ya - xb yb - za wa + zb wb
+        const Fq p2 = sel(imag, nzo, nzm), q2 = sel(imag, nzm, zo);                // imag: xa yb + xb ya - za wb - zb wa
+        return Fq::dot4(p, ym, q, yo, p2, wm, q2, wo);
+#else
+        return mul(xm, xo, ym, yo) - mul(zm, zo, wm, wo);
+#endif
     }
     B200_DEV Fq one() const { return imag ? Fq::zero() : Fq::one(); }
     B200_DEV HalfXYZZ inf() const { return HalfXYZZ{Fq::zero(), one(), Fq::zero(), Fq::zero()}; }
@@ -97,7 +112,7 @@ static B200_DEV void pair_add_mixed(const PairLane<MODE>& ln, HalfXYZZ& a, const
     const Fq Q = ln.mul(a.X, ln.other(a.X), PP, PPo);
     const Fq X3 = ln.sqr(R, Ro) - PPP - Q.dbl();
     const Fq D = Q - X3;
-    a.Y = ln.mul(R, Ro, D, ln.other(D)) - ln.mul(a.Y, ln.other(a.Y), PPP, PPPo);
+    a.Y = ln.diff(R, Ro, D, ln.other(D), a.Y, ln.other(a.Y), PPP, PPPo);
     a.X = X3;
     a.ZZ = ln.mul(a.ZZ, zzo, PP, PPo);
     a.ZZZ = ln.mul(a.ZZZ, zzzo, PPP, PPPo);
@@ -145,7 +160,7 @@ static B200_DEV void pair_add_full(const PairLane<MODE>& ln, HalfXYZZ& a, const 
     const Fq Q = ln.mul(U1, ln.other(U1), PP, PPo);
     const Fq X3 = ln.sqr(R, Ro) - PPP - Q.dbl();
     const Fq D = Q - X3;
-    a.Y = ln.mul(R, Ro, D, ln.other(D)) - ln.mul(S1, ln.other(S1), PPP, PPPo);
+    a.Y = ln.diff(R, Ro, D, ln.other(D), S1, ln.other(S1), PPP, PPPo);
     a.X = X3;
     const Fq Z2 = ln.mul(a.ZZ, azo, b.ZZ, bzo);
     a.ZZ = ln.mul(Z2, ln.other(Z2), PP, PPo);
