@@ -359,8 +359,8 @@ int b200_imad_peak(b200_ctx* ctx, int reps, double* macs_per_s) {
 
 // ------------------------------------------------------------------------------------------------ sub-operations
 int b200_field_op(b200_ctx* ctx, int field, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n) {
-    if (!ctx || !a || !out || field < 0 || field > 1 || op < 0 || op > 9) return B200_ERR_ARG;
-    if ((op <= 2 || op == 9) && !b) return B200_ERR_ARG;
+    if (!ctx || !a || !out || field < 0 || field > 1 || op < 0 || op > 11) return B200_ERR_ARG;
+    if ((op <= 2 || op >= 9) && !b) return B200_ERR_ARG;
     return Guard{ctx}.run([&] {
         DevBuf da(n * 32), db(n * 32), dout(n * 32);
         B200_CUDA_CHECK(cudaMemcpyAsync(da.p, a, n * 32, cudaMemcpyHostToDevice, ctx->stream));

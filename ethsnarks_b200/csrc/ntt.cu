@@ -415,6 +415,8 @@ __global__ void field_op_kernel(int op, const F* __restrict__ a, const F* __rest
         case 6: r = x.sqr(); break;
         case 8: r = x.inv_binary(); break;
         case 9: r = F::dot2(x, b[i], b[i], b[i]); break;   // a b + b^2 under one reduction
+        case 10: { const F nx = x.neg_lazy(); r = F::dot4(x, b[i], x, b[i], nx, nx, b[i], b[i]); break; }   // (a + b)^2; a = 0 feeds p * p
+        case 11: r = diff_of_products(x, x, b[i], b[i]); break;                                             // a^2 - b^2 as the XYZZ additions use it
         default: r = x.neg(); break;
     }
     out[i] = r;

@@ -17,7 +17,7 @@ u32p = C.POINTER(C.c_uint32)
 u8p = C.POINTER(C.c_uint8)
 
 FMT_MCL_NOZK, FMT_MCL_FULL, FMT_ALT_NOZK, FMT_ALT_FULL, FMT_CACHE = 0, 1, 2, 3, 4
-OP_MUL, OP_ADD, OP_SUB, OP_TO_MONT, OP_FROM_MONT, OP_INV, OP_SQR, OP_NEG, OP_INV_BINARY, OP_DOT2 = range(10)
+OP_MUL, OP_ADD, OP_SUB, OP_TO_MONT, OP_FROM_MONT, OP_INV, OP_SQR, OP_NEG, OP_INV_BINARY, OP_DOT2, OP_DOT4, OP_DIFF = range(12)
 NTT_FFT, NTT_IFFT, NTT_COSET_FFT, NTT_ICOSET_FFT = range(4)
 
 # every symbol include/b200snark.h declares (tests check the .so exports all of them)

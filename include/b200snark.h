@@ -42,7 +42,9 @@ enum { B200_OK = 0, B200_ERR_CUDA = 1, B200_ERR_ARG = 2, B200_ERR_FORMAT = 3, B2
 enum { B200_FMT_MCL_NOZK = 0, B200_FMT_MCL_FULL = 1, B200_FMT_ALT_NOZK = 2, B200_FMT_ALT_FULL = 3,
        B200_FMT_CACHE = 4 /* device-native key cache written by b200_key_export */ };
 enum { B200_OP_MUL = 0, B200_OP_ADD = 1, B200_OP_SUB = 2, B200_OP_TO_MONT = 3, B200_OP_FROM_MONT = 4, B200_OP_INV = 5, B200_OP_SQR = 6, B200_OP_NEG = 7, B200_OP_INV_BINARY = 8,
-       B200_OP_DOT2 = 9 /* a*b + b*b with one Montgomery reduction (the fused row product of the paired G2 kernel) */ };
+       B200_OP_DOT2 = 9 /* a*b + b*b with one Montgomery reduction (the fused row product of the paired G2 kernel) */,
+       B200_OP_DOT4 = 10 /* (a + b)^2 as FOUR products a*b + a*b + (p-a)*(p-a) + b*b under one reduction (the Y3 row set of the paired G2 kernel) */,
+       B200_OP_DIFF = 11 /* a*a - b*b as one two-product row set (the Y3 of every G1 XYZZ addition) */ };
 enum { B200_NTT_FFT = 0, B200_NTT_IFFT = 1, B200_NTT_COSET_FFT = 2, B200_NTT_ICOSET_FFT = 3 };
 
 /* One R1CS matrix in CSR form: row i holds sum_k coeff_table[coeff_idx[k]] * w[col[k]], k in [row_ptr[i], row_ptr[i+1]).

@@ -36,6 +36,14 @@ def test_field_ops(ctx, field, p):
     a2, b2 = np.concatenate([a, top]), np.concatenate([b, top])
     mul, add = getattr(orc, name + "_mul"), getattr(orc, name + "_add")
     assert np.array_equal(ctx.field_op(field, L.OP_DOT2, a2, b2), add(mul(a2, b2), mul(b2, b2)))
+    # the Y3 row sets of the XYZZ additions: four products under one reduction (operands up to p itself: a = 0 enters as p * p,
+    # a = b = p - 1 gives three products of (p-1)^2), and the two-product difference
+    a3 = np.concatenate([a2, orc.ints_to_arr([0, p - 1, 0])])
+    b3 = np.concatenate([b2, orc.ints_to_arr([p - 1, 0, 0])])
+    sub = getattr(orc, name + "_sub")
+    s3 = add(a3, b3)
+    assert np.array_equal(ctx.field_op(field, L.OP_DOT4, a3, b3), mul(s3, s3))
+    assert np.array_equal(ctx.field_op(field, L.OP_DIFF, a3, b3), sub(mul(a3, a3), mul(b3, b3)))
 
 
 def test_fixed_base_and_group_law(ctx):

@@ -195,3 +195,37 @@ def test_pk_bellman2ethsnarks_matches_the_oracle_key():
     assert pos[0] == len(full)
     assert H.pk_bellman2ethsnarks(json.dumps(d)) == k.serialize(orc.FMT_ALT_NOZK)
     assert H.pk_bellman2ethsnarks(d, alt=False) == k.serialize(orc.FMT_MCL_NOZK)
+
+
+def test_multi_product_montgomery_rows_stay_inside_their_accumulators():
+    """Big-integer model of the row sets in ethsnarks_b200/csrc/fp.cuh (Fp::dot2 / Fp::dot4): K products summed before each
+    row's m*p step.  The accumulators hold 288 bits before the shift and the result must come out below 2p (one conditional
+    subtraction).  Checked for both moduli at the largest operands the kernels feed (p itself, from neg_lazy of zero) and on
+    random ones; the value is checked too.  The bound FAILS at K = 6 for Fq, which the test also pins."""
+    import random
+    rng = random.Random(5)
+    for p in (orc.R_MOD, orc.Q_MOD):
+        inv = (-pow(p, -1, 1 << 32)) % (1 << 32)
+        R = 1 << 256
+
+        def rows(pairs):
+            T, worst = 0, 0
+            for i in range(8):
+                for a, b in pairs:
+                    T += a * ((b >> (32 * i)) & 0xffffffff)
+                T += (((T & 0xffffffff) * inv) & 0xffffffff) * p
+                worst = max(worst, T)
+                assert T & 0xffffffff == 0
+                T >>= 32
+            return T, worst
+
+        for K in (2, 4):
+            cases = [[(p, p)] * K, [(p - 1, p - 1)] * K, [(p, p - 1)] * K]
+            cases += [[(rng.randrange(p + 1), rng.randrange(p + 1)) for _ in range(K)] for _ in range(300)]
+            for pairs in cases:
+                T, worst = rows(pairs)
+                assert worst < 1 << 288
+                assert T < 2 * p
+                assert T % p == sum(a * b for a, b in pairs) * pow(R, -1, p) % p
+        if p == orc.Q_MOD:
+            assert rows([(p, p)] * 6)[0] >= 2 * p   # six products would need a second subtraction: dot4 is the limit used
