@@ -39,9 +39,9 @@ MAC_PER_G2_ADD = 2 * (6 * 200 + 2 * 136 + 328)
 BYTES_PER_G1_POINT = 96      # 64 B affine base + 32 B scalar
 BYTES_PER_G2_POINT = 160
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the accumulate kernel at 2^20 points, from the ncu --set full
-# capture summarised in profiles/r1_ncu_msm_accumulate_2p20_full.csv (window tables: 13 table points are read per scalar,
+# capture summarised in profiles/r2_ncu_accumulate_fused_y.txt (window tables: 13 table points are read per scalar,
 # so the traffic is ~12x the canonical 96/160 B per point; HBM stays under 11 % busy)
-NCU_TRAFFIC_BYTES = {("G2", 20): 1.880513e9 + 0.169542e9, ("G1", 20): 1.854417e9 + 0.102273e9}   # profiles/r1_ncu_msm_accumulate_2p20_v2.csv
+NCU_TRAFFIC_BYTES = {("G2", 20): 1.881476e9 + 0.169665e9, ("G1", 20): 1.853902e9 + 0.101182e9}
 
 
 def table_windows(n, override=0):
