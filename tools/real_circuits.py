@@ -24,8 +24,15 @@ import ethsnarks_b200 as eb  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--window", type=int, default=0, help="window size c of the fixed-base tables (0 = cost model)")
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value, repeatable")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the reference CPU prover (window sweeps)")
     args = ap.parse_args()
     ctx = eb.Context(0)
+    if args.window:
+        ctx.set_option("window", args.window)
+    for kv in args.opt:
+        ctx.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     for name in ("mimc_merkle", "sha256", "eddsa"):
         circ, w, _ = orc_ref.reference_circuit(name)
         gold = json.load(open(os.path.join(ROOT, "tests", "golden", "circuit_%s.json" % name)))
@@ -45,8 +52,8 @@ def main():
         timeline = [(n, round(a, 3), round(d, 3)) for n, a, d in ctx.timeline()]
         ones = int(np.sum(np.all(w == np.asarray(orc.constants()[8:12], np.uint64), axis=1)))
         zeros = int(np.sum(~w.any(axis=1)))
-        cpu = orc_ref.prove(circ, w, key, repeats=4, threads=os.cpu_count(), all_times=True)[2][1:]
-        print(json.dumps({"circuit": name, "constraints": circ.nc, "variables": circ.nv, "domain": circ.m,
+        cpu = [float("nan")] if args.no_cpu else orc_ref.prove(circ, w, key, repeats=4, threads=os.cpu_count(), all_times=True)[2][1:]
+        print(json.dumps({"circuit": name, "window": args.window, "constraints": circ.nc, "variables": circ.nv, "domain": circ.m,
                           "witness_zero_or_one": (zeros + ones) / float(circ.nv + 1),
                           "gpu_prove_wall_ms_median": float(np.median(wall)), "gpu_prove_device_ms_median": float(np.median(dev)),
                           "reference_cpu_prove_ms_median": float(np.median(cpu)) * 1e3, "cpu_threads": os.cpu_count(),
