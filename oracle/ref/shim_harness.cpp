@@ -11,6 +11,12 @@
 //   shim_prove genkeys <sha256|mimc_merkle|eddsa> <pk_out> <vk_out.json> <proof_out.json>
 //       stub_genkeys_from_pb on the device, then the reference's loader reads the pk file back, the GPU proves with it and
 //       the reference verifier accepts the proof under the generated vk
+//   shim_prove verify  <vk.json> <proof.json>
+//       the drop-in's stub_main_verify (src/stubs.cpp:90-132) with the same argv convention; host only, no GPU needed
+//   shim_prove selftest <sha256|mimc_merkle|eddsa> - -
+//       the drop-in's stub_test_proof_verify (src/stubs.cpp:135-149), the call the reference's gadget tests end with: keys and
+//       proof from the device, the reference's verifier on the host; also run on a protoboard whose first public input was
+//       changed after the witness was made (must be rejected)
 // Prints one "key: value" line per fact; exit code 0 only if every check holds.
 #include "circuits.hpp"
 #include "ethsnarks_b200.hpp"
@@ -42,6 +48,15 @@ static int run(ProtoboardT& pb, const char*) {
     const auto& cs = pb.constraint_system;
     std::cout << "constraints: " << cs.num_constraints() << "\nvariables: " << cs.num_variables() << "\ninputs: " << cs.num_inputs() << "\n";
     int bad = 0;
+    if (g_mode == "selftest") {
+        const bool ok = stub_test_proof_verify(pb);
+        std::cout << "stub_test_proof_verify: " << ok << "\n";
+        pb.values[0] += FieldT::one();               // variable 1 = the first public input (a protoboard cannot be copied)
+        const bool rejected = !stub_test_proof_verify(pb);
+        pb.values[0] -= FieldT::one();
+        std::cout << "stub_test_proof_verify_rejects_wrong_input: " << rejected << "\n";
+        return !ok + !rejected;
+    }
     std::string pk_file = g_a, vk_json, proof_out;
     if (g_mode == "genkeys") {
         auto t0 = std::chrono::steady_clock::now();
@@ -91,6 +106,12 @@ static int run(ProtoboardT& pb, const char*) {
 }
 
 int main(int argc, char** argv) {
+    if (argc == 4 && std::string(argv[1]) == "verify") {
+        const char* av[3] = {"verify", argv[2], argv[3]};
+        const int rc = stub_main_verify("shim_prove", 3, av);
+        std::cout << "stub_main_verify_rc: " << rc << "\n";
+        return rc;
+    }
     if (argc < 5) { std::cerr << "usage: shim_prove prove <circuit> <pk> <proof_out> [vk.json] | genkeys <circuit> <pk_out> <vk_out> <proof_out>\n"; return 2; }
     g_mode = argv[1];
     g_a = argv[3]; g_b = argv[4];

@@ -4,12 +4,16 @@
 #include "b200snark.h"
 #include "utils.hpp"          // the reference's loadFromFile / writeToFile (src/utils.hpp:166-185)
 #include "export.hpp"         // the reference's proof_to_json / vk2json_file declarations (src/export.hpp)
+#include "import.hpp"         // the reference's vk_from_json / proof_from_json declarations (src/import.hpp), for stub_verify
 #include <libfqfft/evaluation_domain/domains/basic_radix2_domain.hpp>
 #include <libfqfft/evaluation_domain/domains/recursive_domain.hpp>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
+#include <iostream>
 #include <map>
 #include <mutex>
+#include <sstream>
 #include <stdexcept>
 
 namespace ethsnarks {
@@ -280,10 +284,9 @@ const std::shared_ptr<libfqfft::evaluation_domain<FieldT>> get_domain(Protoboard
 // src/stubs.cpp:77-87 with the generator on the device: the five field elements the reference draws inside
 // r1cs_gg_ppzksnark_zok_generator (…zok.tcc:289-293) are drawn here with the same FieldT::random_element(); the queries come
 // back through the key cache blob (b200_key_export) and are written in the reference's own pk / vk.json formats.
-int stub_genkeys_from_pb(ProtoboardT& pb, const char* pk_file, const char* vk_file) {
+static int generate_keys(const libsnark::r1cs_constraint_system<FieldT>& cs, ProvingKeyT& pk, VerificationKeyT& vkey) {
     std::lock_guard<std::mutex> lock(g_mu);
     b200_ctx* ctx = context();
-    const auto& cs = pb.constraint_system;
     const size_t nv = cs.num_variables(), ni = cs.num_inputs();
     FieldT toxic[5];     // t, alpha, beta, gamma, delta
     for (auto& x : toxic) x = FieldT::random_element();
@@ -316,7 +319,7 @@ int stub_genkeys_from_pb(ProtoboardT& pb, const char* pk_file, const char* vk_fi
     const uint64_t* B = (const uint64_t*)(p + off); off += nB * 128;
     const uint64_t* H = (const uint64_t*)(p + off); off += nH * 64;
     const uint64_t* L = (const uint64_t*)(p + off);
-    ProvingKeyT pk;
+    pk = ProvingKeyT();
     pk.alpha_g1 = g1_from(c1, false, true); pk.beta_g1 = g1_from(c1 + 8, false, true); pk.delta_g1 = g1_from(c1 + 16, false, true);
     pk.beta_g2 = g2_from(c2, false, true); pk.delta_g2 = g2_from(c2 + 16, false, true);
     // the reference keeps only the non-zero entries of A and B (…zok.hpp:218-230, kc_batch_exp)
@@ -334,11 +337,63 @@ int stub_genkeys_from_pb(ProtoboardT& pb, const char* pk_file, const char* vk_fi
     std::vector<G1T> ic_rest;
     for (size_t i = 1; i <= ni; ++i) ic_rest.push_back(g1_from(&vk[56 + 8 * i], all_zero(&vk[56 + 8 * i], 8), true));
     G1T ic0 = g1_from(&vk[56], all_zero(&vk[56], 8), true);
-    VerificationKeyT vkey(g1_from(&vk[0], false, true), g2_from(&vk[8], false, true), g2_from(&vk[24], false, true), g2_from(&vk[40], false, true),
-                          libsnark::accumulation_vector<G1T>(std::move(ic0), std::move(ic_rest)));
+    vkey = VerificationKeyT(g1_from(&vk[0], false, true), g2_from(&vk[8], false, true), g2_from(&vk[24], false, true), g2_from(&vk[40], false, true),
+                            libsnark::accumulation_vector<G1T>(std::move(ic0), std::move(ic_rest)));
+    return 0;
+}
+
+int stub_genkeys_from_pb(ProtoboardT& pb, const char* pk_file, const char* vk_file) {
+    ProvingKeyT pk;
+    VerificationKeyT vkey;
+    const int rc = generate_keys(pb.constraint_system, pk, vkey);
+    if (rc) return rc;
     vk2json_file(vkey, vk_file);
     writeToFile<ProvingKeyT>(pk_file, pk);
     return 0;
+}
+
+// src/stubs.cpp:135-149 - the call every gadget test of the reference ends with (test/test_*.cpp): keys for the protoboard's
+// constraint system, a proof for its assignment, the verifier's answer.  Here the generator and the prover run on the device
+// and the check is the reference's own verifier on the host; nothing is written to disk.
+bool stub_test_proof_verify(const ProtoboardT& in_pb) {
+    ProvingKeyT pk;
+    VerificationKeyT vkey;
+    const int rc = generate_keys(in_pb.constraint_system, pk, vkey);
+    if (rc) fail("b200_generate_key", rc);
+    struct Release { const ProvingKeyT& k; ~Release() { b200_release(k); } } release{pk};   // the side table is keyed by &pk
+    const ProofT proof = gpu_prove(pk, in_pb.constraint_system, in_pb.values);
+    return libsnark::r1cs_gg_ppzksnark_zok_verifier_strong_IC<ppT>(vkey, in_pb.primary_input(), proof);
+}
+
+// src/stubs.cpp:16-34 - verification stays on the host: the reference's JSON readers (src/import.cpp) and verifier
+bool stub_verify(const char* vk_json, const char* proof_json) {
+    ppT::init_public_params();
+    std::stringstream vk_text(vk_json), proof_text(proof_json);
+    const VerificationKeyT vk = vk_from_json(vk_text);
+    const InputProofPairType input_and_proof = proof_from_json(proof_text);
+    return libsnark::r1cs_gg_ppzksnark_zok_verifier_strong_IC<ppT>(vk, input_and_proof.first, input_and_proof.second);
+}
+
+// src/stubs.cpp:90-132 - same usage line, messages and exit codes (1 usage / rejected proof, 2 unreadable file, 0 accepted)
+int stub_main_verify(const char* prog_name, int argc, const char** argv) {
+    if (argc < 3) {
+        std::cerr << "Usage: " << prog_name << " " << argv[0] << " <vk.json> <proof.json>" << std::endl;
+        return 1;
+    }
+    std::string text[2];
+    for (int i = 0; i < 2; ++i) {
+        std::ifstream in(argv[1 + i]);
+        if (!in) {
+            std::cerr << "Error: cannot open " << argv[1 + i] << std::endl;
+            return 2;
+        }
+        std::stringstream ss;
+        ss << in.rdbuf();
+        text[i] = ss.str();
+    }
+    if (stub_verify(text[0].c_str(), text[1].c_str())) return 0;
+    std::cerr << "Error: failed to verify proof!" << std::endl;
+    return 1;
 }
 
 }  // namespace ethsnarks

@@ -9,6 +9,10 @@
 //   ethsnarks::prove(ProverContextT&, ProtoboardT&)     src/stubs.hpp:19, stubs.cpp:42-47     same signature; proof from the GPU
 //   ethsnarks::stub_genkeys_from_pb(pb, pk, vk)         src/stubs.hpp:16, stubs.cpp:77-87     same signature; keys from the GPU generator,
 //                                                                                           written in the reference's file formats
+//   ethsnarks::stub_test_proof_verify(const ProtoboardT&) src/stubs.hpp:14, stubs.cpp:135-149     same signature; generator and prover on
+//                                                                                           the GPU, the reference's verifier on the host
+//   ethsnarks::stub_verify / stub_main_verify           src/stubs.hpp:10-12, stubs.cpp:16-34,90-132  same signatures; verification stays on
+//                                                                                           the host (the reference's import.cpp + verifier)
 //   libsnark::r1cs_gg_ppzksnark_zok_prover<ppT>(ProverContext<ppT>&, const std::vector<Fr<ppT>>&)
 //                                                       src/r1cs_gg_ppzksnark_zok/r1cs_gg_ppzksnark_zok.tcc:451-550
 //                                                       explicit specialisation for ethsnarks::ppT declared below: every
@@ -39,7 +43,11 @@ r1cs_gg_ppzksnark_zok_proof<ethsnarks::ppT> r1cs_gg_ppzksnark_zok_prover<ethsnar
 
 namespace ethsnarks {
 
-// ---- src/stubs.hpp:16-21, unchanged signatures
+// ---- src/stubs.hpp:10-21, unchanged signatures (stub_genkeys<GadgetT> / stub_main_genkeys<GadgetT> are templates of that
+// header over stub_genkeys_from_pb and work unchanged)
+bool stub_verify(const char* vk_json, const char* proof_json);
+int stub_main_verify(const char* prog_name, int argc, const char** argv);
+bool stub_test_proof_verify(const ProtoboardT& in_pb);
 int stub_genkeys_from_pb(ProtoboardT& pb, const char* pk_file, const char* vk_file);
 ProvingKeyT load_proving_key(const char* pk_file);
 std::string prove(ProverContextT& context, ProtoboardT& pb);

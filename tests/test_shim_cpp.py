@@ -36,6 +36,9 @@ def test_shim_exports_the_reference_entry_points():
         "ethsnarks::load_proving_key(char const*)",
         "ethsnarks::get_domain(libsnark::protoboard<",
         "ethsnarks::stub_genkeys_from_pb(libsnark::protoboard<",
+        "ethsnarks::stub_test_proof_verify(libsnark::protoboard<",
+        "ethsnarks::stub_verify(char const*, char const*)",
+        "ethsnarks::stub_main_verify(char const*, int, char const**)",
         "libsnark::r1cs_gg_ppzksnark_zok_prover<%s>(libsnark::ProverContext<%s>&, std::vector<" % (pp, pp),
         "ethsnarks::proof_to_json[abi:cxx11](",
     ):
@@ -55,6 +58,40 @@ def test_shim_fails_loudly_without_a_gpu():
         res = subprocess.run([SHIM_BIN, "prove", "eddsa", pk, os.path.join(d, "proof.json")], capture_output=True, text=True)
     assert res.returncode != 0
     assert "b200_init" in res.stderr and "no CPU fallback" in res.stderr
+
+
+@needs_shim
+def test_shim_stub_main_verify_on_the_golden_proof():
+    """The drop-in's stub_verify / stub_main_verify (src/stubs.cpp:16-34, 90-132; host only): exit code 0 for the committed
+    golden proof under the oracle key's vk.json, 1 with the reference's message for a changed public input, 2 for an
+    unreadable file, 1 with the usage line for too few arguments."""
+    circ, w, _ = orc_ref.reference_circuit("eddsa")
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "circuit_eddsa.json")))
+    key = orc.Key(circ)
+    with tempfile.TemporaryDirectory() as d:
+        vk, proof, bad = (os.path.join(d, n) for n in ("vk.json", "proof.json", "bad.json"))
+        open(vk, "w").write(key.vk_json())
+        open(proof, "w").write(g["proof_json"])
+        tampered = json.loads(g["proof_json"])
+        tampered["input"][0] = hex(int(tampered["input"][0], 16) ^ 1)
+        open(bad, "w").write(json.dumps(tampered))
+        ok = subprocess.run([SHIM_BIN, "verify", vk, proof], capture_output=True, text=True)
+        assert ok.returncode == 0 and _facts(ok.stdout)["stub_main_verify_rc"] == "0", ok.stdout + ok.stderr
+        rej = subprocess.run([SHIM_BIN, "verify", vk, bad], capture_output=True, text=True)
+        assert rej.returncode == 1 and "Error: failed to verify proof!" in rej.stderr
+        missing = subprocess.run([SHIM_BIN, "verify", vk, os.path.join(d, "absent.json")], capture_output=True, text=True)
+        assert missing.returncode == 2 and "Error: cannot open" in missing.stderr
+
+
+@pytest.mark.gpu
+@needs_shim
+def test_shim_stub_test_proof_verify_on_device():
+    """stub_test_proof_verify (src/stubs.cpp:135-149), the call the reference's gadget tests end with: generator and prover
+    on the device, the reference's verifier on the host; a protoboard with a changed public input is rejected."""
+    res = subprocess.run([SHIM_BIN, "selftest", "eddsa", "-", "-"], capture_output=True, text=True)
+    assert res.returncode == 0, res.stdout + res.stderr
+    f = _facts(res.stdout)
+    assert f["stub_test_proof_verify"] == "1" and f["stub_test_proof_verify_rejects_wrong_input"] == "1"
 
 
 @pytest.mark.gpu
